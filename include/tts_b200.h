@@ -1,0 +1,159 @@
+/*
+ * tts_b200 — C ABI of the B200-native MelGAN / MB-MelGAN / FB-MelGAN vocoder inference path.
+ *
+ * The reference (wjqkkky/TTS, Mozilla TTS 0.0.5) has no native boundary for this path: its
+ * "plugin API" is the Python surface of
+ *     TTS/vocoder/models/melgan_generator.py:8-97            (MelganGenerator)
+ *     TTS/vocoder/models/multiband_melgan_generator.py:7-39  (MultibandMelganGenerator)
+ *     TTS/vocoder/models/fullband_melgan_generator.py:6-30   (FullbandMelganGenerator)
+ *     TTS/vocoder/layers/melgan.py:5-45                      (ResidualStack)
+ *     TTS/vocoder/layers/pqmf.py:10-56                       (PQMF)
+ * The functions below are what a maintainer's binding for those classes calls (ctypes stub in
+ * INTEGRATION.md; the shipped binding is tts_b200/_lib.py).  Plain C: pointers, sizes, a stream
+ * handle.  No torch types.  All device pointers are CUDA global-memory pointers on the plan's
+ * device; `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *
+ * Every function returns 0 on success or a negative ttsb200_status; the message of the last
+ * failure on the calling thread is ttsb200_last_error().  Nothing here falls back to the CPU.
+ */
+#ifndef TTS_B200_H_
+#define TTS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define TTSB200_API __attribute__((visibility("default")))
+#else
+#define TTSB200_API
+#endif
+
+#define TTSB200_ABI_VERSION 1
+#define TTSB200_MAX_STAGES 8
+
+typedef enum ttsb200_status {
+  TTSB200_OK = 0,
+  TTSB200_ERR_INVALID = -1,   /* bad argument / unsupported configuration                        */
+  TTSB200_ERR_SHAPE = -2,     /* input too short for the reflect padding (reference raises too)  */
+  TTSB200_ERR_CUDA = -3,      /* a CUDA runtime call failed                                      */
+  TTSB200_ERR_WORKSPACE = -4, /* workspace missing or smaller than ttsb200_workspace_bytes()     */
+  TTSB200_ERR_ARCH = -5       /* device is not sm_100 (the library carries sm_100a code only)    */
+} ttsb200_status;
+
+typedef enum ttsb200_precision {
+  TTSB200_F32 = 0, /* fp32 FFMA path: max-abs waveform error <= 1e-5 vs the reference              */
+  TTSB200_BF16 = 1 /* BF16 operands, fp32 accumulate on tcgen05/TMEM: SNR >= 40 dB vs fp32         */
+} ttsb200_precision;
+
+/* Constructor arguments of the generator classes (melgan_generator.py:9-16,
+ * multiband_melgan_generator.py:8-16, fullband_melgan_generator.py:7-14) plus the PQMF the
+ * multi-band class owns (multiband_melgan_generator.py:24; pqmf.py:11). */
+typedef struct ttsb200_generator_config {
+  int32_t in_channels;      /* mel bins (80)                                                     */
+  int32_t out_channels;     /* 1, or 4 sub-bands for MB-MelGAN                                   */
+  int32_t proj_kernel;      /* odd (7)                                                           */
+  int32_t base_channels;    /* 512 / 384                                                         */
+  int32_t n_stages;         /* len(upsample_factors) <= TTSB200_MAX_STAGES                       */
+  int32_t upsample_factors[TTSB200_MAX_STAGES];
+  int32_t res_kernel;       /* odd (3); block b has dilation res_kernel**b (melgan.py:14)        */
+  int32_t num_res_blocks;
+  int32_t pqmf_bands;       /* 0 = no PQMF; else N (4) and out_channels must equal it            */
+  int32_t pqmf_taps;        /* `taps` of PQMF (62): the synthesis filter has taps+1 coefficients */
+  float act_slope;          /* LeakyReLU slope (0.2)                                             */
+} ttsb200_generator_config;
+
+typedef struct ttsb200_plan ttsb200_plan;       /* immutable after creation; shareable across threads */
+typedef struct ttsb200_profile ttsb200_profile; /* per-launch CUDA-event timings; one user at a time  */
+
+typedef struct ttsb200_forward_args {
+  const float* mel;         /* device, [batch, in_channels, frames] fp32, contiguous             */
+  int32_t batch;
+  int32_t frames;
+  int32_t pad;              /* inference_padding: replicate-pad frames per side                  */
+                            /* (melgan_generator.py:85-88); 0 for forward()                      */
+  int32_t precision;        /* ttsb200_precision                                                 */
+  float* out;               /* device, [batch, 1 or out_channels, ttsb200_output_length()] fp32  */
+  void* workspace;          /* device scratch, >= ttsb200_workspace_bytes(), 256-byte aligned    */
+  size_t workspace_bytes;
+  void* stream;             /* cudaStream_t                                                      */
+  int32_t skip_pqmf;        /* 1: stop after tanh and write the sub-bands (== forward())         */
+  int32_t n_taps;           /* optional: copy outputs of reference `layers[i]` (per-layer parity,*/
+  const int32_t* tap_layers;/*   the indexing of bin/convert_melgan_torch_to_tf.py:89-101)       */
+  float* const* tap_out;    /*   each device [batch, C_i, L_i] fp32                              */
+  ttsb200_profile* profile; /* optional                                                          */
+} ttsb200_forward_args;
+
+TTSB200_API int32_t ttsb200_abi_version(void);
+TTSB200_API const char* ttsb200_last_error(void);
+
+/* Device check: returns 0 when `device` is an sm_100 part this library can run on. */
+TTSB200_API int32_t ttsb200_device_ok(int32_t device);
+
+/* Build a plan from folded (weight-norm removed: w = g*v/||v||, melgan_generator.py:91-97) fp32
+ * HOST tensors, passed in the reference's state_dict() order of parametrised layers:
+ *   layers.1 {weight [C0,in,k], bias}, then for each stage s:
+ *     layers.{3+3s} ConvTranspose1d {weight [Cin,Cout,2f], bias},
+ *     for b in blocks: layers.{4+3s}.blocks.b.2 {weight [C,C,res_kernel], bias}, .blocks.b.4 {weight [C,C,1], bias}
+ *     for b in blocks: layers.{4+3s}.shortcuts.b {weight [C,C,1], bias}
+ *   layers.{4+3S} head {weight [out,Clast,k], bias}
+ *   and, when pqmf_bands > 0, the PQMF synthesis buffer G [1,N,taps+1] (pqmf.py:32,35).
+ * n_tensors must equal ttsb200_expected_tensors(cfg).  Weights are re-laid-out for the kernels
+ * and uploaded to `device`; the host tensors are not referenced after the call returns. */
+TTSB200_API int32_t ttsb200_expected_tensors(const ttsb200_generator_config* cfg);
+TTSB200_API int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* const* tensors,
+                            int32_t n_tensors, int32_t device, ttsb200_plan** out_plan);
+TTSB200_API void ttsb200_plan_destroy(ttsb200_plan* plan);
+
+/* Samples per item: (frames + 2*pad) * prod(upsample_factors) * (pqmf_bands or 1). */
+TTSB200_API int64_t ttsb200_output_length(const ttsb200_plan* plan, int32_t frames, int32_t pad, int32_t skip_pqmf);
+TTSB200_API int64_t ttsb200_workspace_bytes(const ttsb200_plan* plan, int32_t batch, int32_t frames, int32_t pad,
+                                int32_t precision);
+/* Shape [batch, C_i, L_i] of reference layers[layer] output, for sizing tap buffers. */
+TTSB200_API int32_t ttsb200_layer_shape(const ttsb200_plan* plan, int32_t layer, int32_t frames, int32_t pad,
+                            int32_t* channels, int64_t* length);
+
+/* generator.inference(mel) / generator.forward(mel): asynchronous on args->stream, device buffers. */
+TTSB200_API int32_t ttsb200_generator_forward(const ttsb200_plan* plan, const ttsb200_forward_args* args);
+
+/* Same with HOST buffers (pageable or pinned): copies mel in, runs, copies the waveform out and
+ * synchronises — the call TTS/server/synthesizer.py:153-159 amounts to.  Uses plan-owned device
+ * and pinned staging buffers (serialised by a mutex). */
+TTSB200_API int32_t ttsb200_generator_forward_host(ttsb200_plan* plan, const float* mel_host, int32_t batch,
+                                       int32_t frames, int32_t pad, int32_t precision,
+                                       float* out_host);
+
+/* PQMF.synthesis(x) (pqmf.py:51-56): x [batch, N, Ts] -> y [batch, 1, N*Ts + 2*(taps/2) - taps].
+ * G is the module's device buffer [1, N, taps+1]. */
+TTSB200_API int32_t ttsb200_pqmf_synthesis(const float* x, const float* G, int32_t batch, int32_t bands,
+                               int32_t taps, int64_t Ts, float* y, void* stream);
+/* PQMF.analysis(x) (pqmf.py:48-49): x [batch, 1, T] -> y [batch, N, (T + 2*(taps/2) - taps - 1)/N + 1].
+ * H is the module's device buffer [N, 1, taps+1]. */
+TTSB200_API int32_t ttsb200_pqmf_analysis(const float* x, const float* H, int32_t batch, int32_t bands,
+                              int32_t taps, int64_t T, float* y, void* stream);
+
+/* Per-launch timing.  Attach via args->profile; after the stream has been synchronised,
+ * ttsb200_profile_read() returns one record per kernel launched since the last reset. */
+typedef struct ttsb200_launch_record {
+  const char* name;   /* static string: kernel family + role, e.g. "f32.resblock.conv2+shortcut" */
+  int32_t layer;      /* reference layers[i] index the launch belongs to                         */
+  float ms;           /* CUDA-event duration on the launch stream                                */
+  double flops;       /* algorithmic FLOPs of the launch (2 x MACs)                              */
+  double bytes;       /* algorithmic HBM bytes (inputs read once + outputs written once)         */
+} ttsb200_launch_record;
+
+TTSB200_API int32_t ttsb200_profile_create(ttsb200_profile** out_profile);
+TTSB200_API void ttsb200_profile_destroy(ttsb200_profile* profile);
+TTSB200_API void ttsb200_profile_reset(ttsb200_profile* profile);
+TTSB200_API int32_t ttsb200_profile_read(ttsb200_profile* profile, ttsb200_launch_record* records, int32_t max_records);
+
+/* Number of kernels one ttsb200_generator_forward() launches for this shape (bench "gpu_launches"). */
+TTSB200_API int32_t ttsb200_launch_count(const ttsb200_plan* plan, int32_t precision, int32_t skip_pqmf);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TTS_B200_H_ */

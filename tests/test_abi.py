@@ -1,0 +1,69 @@
+"""The C-ABI library loads on a CPU-only box and exports every symbol include/tts_b200.h declares.
+No compute calls here (no GPU)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from tts_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "tts_b200.h")).read()
+    return sorted(set(re.findall(r"TTSB200_API[^;(]*?\b(ttsb200_\w+)\s*\(", text)))
+
+
+def test_header_and_binding_agree():
+    syms = header_symbols()
+    assert len(syms) >= 18
+    assert sorted(_lib.SYMBOLS) == syms
+
+
+def test_library_exports_every_symbol():
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in header_symbols():
+        assert hasattr(lib, name), name
+    assert _lib.load().ttsb200_abi_version() == _lib.ABI_VERSION
+
+
+def test_struct_layout_matches_header(tmp_path):
+    """Compile the header as plain C with gcc and compare sizeof/offsetof with the ctypes mirror."""
+    import subprocess
+    src = tmp_path / "sz.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "tts_b200.h"\n'
+        'int main(void){printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(ttsb200_generator_config),'
+        'sizeof(ttsb200_forward_args), sizeof(ttsb200_launch_record), offsetof(ttsb200_forward_args, out),'
+        'offsetof(ttsb200_forward_args, tap_layers), offsetof(ttsb200_forward_args, profile));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           str(src), "-o", str(exe)])
+    got = [int(v) for v in subprocess.check_output([str(exe)]).split()]
+    F = _lib.ForwardArgs
+    assert got == [ctypes.sizeof(_lib.GeneratorConfig), ctypes.sizeof(F), ctypes.sizeof(_lib.LaunchRecord),
+                   F.out.offset, F.tap_layers.offset, F.profile.offset]
+
+
+def test_argument_validation_without_gpu():
+    lib = _lib.load()
+    cfg = _lib.GeneratorConfig()
+    assert lib.ttsb200_expected_tensors(None) < 0
+    assert "NULL" in _lib.last_error()
+    cfg.n_stages, cfg.num_res_blocks, cfg.pqmf_bands = 4, 3, 4
+    assert lib.ttsb200_expected_tensors(ctypes.byref(cfg)) == 2 * (2 + 4 * 10) + 1
+    h = ctypes.c_void_p()
+    assert lib.ttsb200_plan_create(ctypes.byref(cfg), None, 0, 0, ctypes.byref(h)) < 0
+    with pytest.raises(RuntimeError):
+        _lib.check(lib.ttsb200_generator_forward(None, None))
+    assert lib.ttsb200_output_length(None, 1, 0, 0) < 0
+
+
+def test_sass_is_sm100a_only():
+    """The shipped binary carries sm_100a code and nothing else (no multi-arch fallback)."""
+    import subprocess
+    out = subprocess.run(["cuobjdump", "-lelf", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs

@@ -1,0 +1,212 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle, on a real B200.  -m gpu.
+
+Bars (BASELINE.json north_star): fp32 path max-abs waveform error <= 1e-5; BF16 path SNR >= 40 dB
+against the fp32 reference.
+"""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.melgan_oracle import (GeneratorSpec, generator_inference, pqmf_analysis, pqmf_filters, pqmf_synthesis,
+                                  random_state_dict)
+from tts_b200.vocoder.layers.pqmf import PQMF
+from tts_b200.vocoder.models.fullband_melgan_generator import FullbandMelganGenerator
+from tts_b200.vocoder.models.melgan_generator import MelganGenerator
+from tts_b200.vocoder.models.multiband_melgan_generator import MultibandMelganGenerator
+
+pytestmark = pytest.mark.gpu
+F32_TOL = 1e-5
+CLS = {"melgan": MelganGenerator, "multiband": MultibandMelganGenerator, "fullband": FullbandMelganGenerator}
+
+
+def build(cls, spec_kw, seed, weight_norm=False):
+    """Boundary module on cuda:0 carrying oracle-seeded weights (strict load_state_dict)."""
+    spec = getattr(GeneratorSpec, cls)(**spec_kw)
+    sd = random_state_dict(spec, seed, weight_norm=weight_norm)
+    m = CLS[cls](**spec_kw)
+    if not weight_norm:
+        m.remove_weight_norm()
+    m.load_state_dict(sd, strict=True)
+    return m.cuda().eval(), spec, sd
+
+
+def snr_db(ref, got):
+    ref = ref.double(); got = got.double()
+    return float(10 * torch.log10((ref ** 2).sum() / ((ref - got) ** 2).sum()))
+
+
+CASES = [
+    ("melgan", {}, 1, 200, 2),                                              # BASELINE config 1
+    ("multiband", {}, 2, 64, 2),
+    ("multiband", {}, 1, 100, 0),                                           # server / notebooks set p = 0
+    ("fullband", {"upsample_factors": (5, 5, 4, 3)}, 1, 24, 2),             # odd factors (config 5 model)
+    ("multiband", {"upsample_factors": (8, 4, 2), "num_res_blocks": 4}, 1, 40, 0),   # shipped config
+    ("melgan", {"in_channels": 8, "base_channels": 32, "upsample_factors": (2, 3), "num_res_blocks": 2}, 3, 12, 2),
+    ("melgan", {"in_channels": 13, "base_channels": 40, "upsample_factors": (3,), "num_res_blocks": 1}, 2, 37, 1),
+]
+
+
+@pytest.mark.parametrize("cls,kw,B,T,p", CASES)
+def test_fp32_end_to_end_and_per_layer(cls, kw, B, T, p):
+    m, spec, sd = build(cls, kw, seed=11)
+    m.inference_padding = p
+    g = torch.Generator().manual_seed(5)
+    mel = torch.randn(B, spec.in_channels, T, generator=g)
+    taps_ref = {}
+    ref = generator_inference(spec, sd, mel, p, taps=taps_ref)
+    layers = [1] + [spec.idx_upsample(s) for s in range(spec.n_stages)] + \
+             [spec.idx_stack(s) for s in range(spec.n_stages)] + [spec.idx_head() + 1]
+    out, taps = m.inference_with_taps(mel, layers)          # CPU mel: inference() moves it (synthesize.py:27)
+    torch.cuda.synchronize()
+    assert out.shape == ref.shape and out.dtype == torch.float32 and out.is_cuda
+    for i in layers:                                        # per layer first (convert_melgan_torch_to_tf.py:89-101)
+        err = float((taps[i].cpu() - taps_ref[i]).abs().max())
+        assert err <= F32_TOL, (i, err)
+    err = float((out.cpu() - ref).abs().max())
+    assert err <= F32_TOL, err
+
+
+def test_weight_norm_checkpoint_form():
+    m, spec, sd = build("multiband", {}, seed=3, weight_norm=True)
+    mel = torch.randn(1, 80, 30)
+    ref = generator_inference(spec, sd, mel, 2)
+    a = m.inference(mel).cpu()
+    m.remove_weight_norm()                                  # synthesizer.py:85 sequence
+    b = m.inference(mel).cpu()
+    assert float((a - ref).abs().max()) <= F32_TOL
+    assert torch.equal(a, b)                                # fold before == fold after
+
+
+def test_golden_cfg1_and_cfg2_item(golden):
+    """Against the committed outputs of the unmodified reference."""
+    for name, cls in (("melgan_cfg1", "melgan"), ("mb_cfg2_item", "multiband"), ("mb_shipped", "multiband")):
+        g = golden(name)
+        kw = json.loads(str(g["kw"]))
+        torch.manual_seed(54321)
+        m = CLS[cls](**kw)
+        m.remove_weight_norm()
+        m = m.cuda().eval()
+        m.inference_padding = int(g["p"])
+        torch.manual_seed(1234)
+        mel = torch.randn(int(g["B"]), 80, int(g["T"]))
+        out = m.inference(mel).cpu().numpy()
+        assert tuple(out.shape) == tuple(g["out_shape"])
+        err = np.abs(out[..., ::int(g["sub"])] - g["out"]).max()
+        assert err <= F32_TOL, (name, err)
+
+
+def test_reference_shape_test_on_gpu():
+    """tests/test_vocoder_melgan_generator.py:6-13, eval-mode forward + inference through the kernels."""
+    m = MelganGenerator().cuda().eval()
+    x = torch.rand((4, 80, 64))
+    assert m(x.cuda()).shape == (4, 1, 64 * 256)
+    assert m.inference(x).shape == (4, 1, (64 + 4) * 256)
+
+
+def test_forward_equals_inference_without_padding():
+    m, spec, sd = build("multiband", {}, seed=4)
+    mel = torch.randn(2, 80, 20).cuda()
+    m.inference_padding = 0
+    sub = m(mel)                                            # eval forward: sub-bands, no PQMF
+    assert sub.shape == (2, 4, 20 * 64)
+    full = m.inference(mel)
+    assert torch.equal(m.pqmf_synthesis(sub), full)
+
+
+def test_too_short_input_raises_like_reference():
+    m = MelganGenerator().cuda().eval()
+    m.inference_padding = 0
+    with pytest.raises(RuntimeError, match="Padding size"):
+        m.inference(torch.rand(1, 80, 3))
+    m.inference_padding = 2
+    assert m.inference(torch.rand(1, 80, 1)).shape == (1, 1, 5 * 256)
+
+
+@pytest.mark.parametrize("B,Ts", [(1, 1), (2, 100), (3, 511), (1, 512), (2, 513), (1, 5000)])
+def test_pqmf_synthesis(B, Ts):
+    H, G, U = pqmf_filters()
+    x = torch.randn(B, 4, Ts, generator=torch.Generator().manual_seed(Ts))
+    ref = pqmf_synthesis(x, G, U)
+    pq = PQMF().cuda()
+    y = pq.synthesis(x.cuda()).cpu()
+    assert y.shape == ref.shape
+    assert float((y - ref).abs().max()) <= F32_TOL
+
+
+def test_pqmf_synthesis_golden_and_analysis(golden):
+    g = golden("pqmf")
+    pq = PQMF().cuda()
+    assert np.array_equal(pq.G.cpu().numpy(), g["G"]) and np.array_equal(pq.H.cpu().numpy(), g["H"])
+    y = pq.synthesis(torch.from_numpy(g["syn_in"]).cuda()).cpu().numpy()
+    assert np.abs(y - g["syn_out"]).max() <= F32_TOL
+    a = pq.analysis(torch.from_numpy(g["ana_in"]).cuda()).cpu().numpy()
+    assert a.shape == g["ana_out"].shape and np.abs(a - g["ana_out"]).max() <= F32_TOL
+    assert pq(torch.from_numpy(g["ana_in"]).cuda()).shape == a.shape      # forward == analysis (pqmf.py:45-46)
+
+
+def test_pqmf_generic_bands():
+    """Non-default PQMF(N, taps) goes through the generic kernel."""
+    from oracle.melgan_oracle import pqmf_filters as pf
+    H, G, U = pf(N=2, taps=30, cutoff=0.3, beta=7.0)
+    x = torch.randn(2, 2, 77)
+    ref = pqmf_synthesis(x, G, U)
+    pq = PQMF(N=2, taps=30, cutoff=0.3, beta=7.0).cuda()
+    assert float((pq.synthesis(x.cuda()).cpu() - ref).abs().max()) <= F32_TOL
+    xa = torch.randn(2, 1, 301)
+    assert float((pq.analysis(xa.cuda()).cpu() - pqmf_analysis(xa, H)).abs().max()) <= F32_TOL
+
+
+def test_full_size_properties_cfg2():
+    """BASELINE config 2 at full size (16 x 862 frames): properties that need no full oracle run."""
+    m, spec, sd = build("multiband", {}, seed=21)
+    g = torch.Generator().manual_seed(9)
+    mel = torch.randn(16, 80, 862, generator=g).cuda()
+    out = m.inference(mel)
+    assert out.shape == (16, 1, 866 * 256)
+    assert bool(torch.isfinite(out).all()) and float(out.abs().max()) <= 1.5
+    # batch independence: item 5 alone == item 5 in the batch (bitwise; no cross-item reduction exists)
+    one = m.inference(mel[5:6])
+    assert torch.equal(one[0], out[5])
+    # determinism
+    assert torch.equal(m.inference(mel), out)
+    # oracle on one item
+    ref = generator_inference(spec, sd, mel[5:6].cpu(), 2)
+    assert float((one.cpu() - ref).abs().max()) <= F32_TOL
+    # shift equivariance away from the edges: delaying the mel by 3 frames delays the audio by 3*256
+    m.inference_padding = 0
+    a = m.inference(mel[:1, :, 0:400])
+    b = m.inference(mel[:1, :, 3:403])
+    R = 16 * 256
+    assert float((a[..., 3 * 256 + R:-R] - b[..., R:-(3 * 256 + R)]).abs().max()) <= 2e-6
+
+
+def test_host_buffer_entry_point():
+    m, spec, sd = build("multiband", {}, seed=8)
+    mel = torch.randn(2, 80, 33)
+    dev = m.inference(mel).cpu()
+    host = m._get_engine().forward_host(mel, m.inference_padding)
+    assert torch.equal(dev, host)
+
+
+def test_streams_and_threads():
+    """Flask threads share one module (server.py:64,82): concurrent calls on separate streams agree."""
+    import threading
+    m, spec, sd = build("melgan", {}, seed=2)
+    mels = [torch.randn(1, 80, 50 + 7 * i) for i in range(4)]
+    want = [m.inference(x).cpu() for x in mels]
+    got = [None] * 4
+
+    def work(i):
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                y = m.inference(mels[i])
+            s.synchronize()
+            got[i] = y.cpu()
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    for w, g_ in zip(want, got):
+        assert torch.equal(w, g_)

@@ -1,0 +1,76 @@
+// Shared host/device helpers for the tts_b200 CUDA library (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/tts_b200.h"
+
+namespace ttsb {
+
+// ---- error plumbing (thread-local message behind ttsb200_last_error) -------------------------
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+
+#define TTSB_CUDA(expr)                                                                        \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess)                                                                     \
+      return ::ttsb::fail(TTSB200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+  } while (0)
+
+static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+static inline int ceil_div(int64_t x, int64_t m) { return (int)((x + m - 1) / m); }
+
+// ---- fp32 implicit-GEMM convolution (conv_f32.cu) ---------------------------------------------
+// One launch computes, for every batch item b, GEMM-time index t in [0, Lt) and channel o:
+//   out[b][o][t*out_stride + out_offset] =
+//       epi( bias[o] + sum_{s<nsrc} sum_{j<taps_s} sum_{c<C_s} w_s[ph][j][c][o] * pro_s( x_s[b][c][pos_s(t,j)] ) )
+// pos_s(t,j) = t + j*dil_s + shift_s (+ phase-dependent shift for transposed-conv phases) and
+// is resolved by the edge rule: reflect (ReflectionPad1d), then optional replicate clamp
+// (inference_padding), or zero-fill (transposed conv).
+struct ConvSrc {
+  const float* x;         // [B][C][Lreal]
+  const float* w;         // [phases][taps][C][CoutPad]   (o contiguous)
+  int64_t batch_stride;   // C * Lreal
+  int C;
+  int L;                  // virtual length seen by the reflect rule (= Lreal + 2*clamp_pad)
+  int Lreal;              // stored row length
+  int clamp_pad;          // replicate padding folded into the index map (0 = none)
+  int taps;
+  int dil;
+  int shift;
+  int edge_zero;          // 0: reflect, 1: zero-fill outside [0, L)
+  int lrelu;              // apply LeakyReLU(slope) to the loaded value
+};
+
+struct ConvParams {
+  ConvSrc src[2];
+  int nsrc;
+  const float* bias;      // [CoutPad]
+  float* out;             // [B][Cout][out_L]
+  int64_t out_batch_stride;
+  int Cout;
+  int CoutPad;
+  int Lt;                 // GEMM-time extent
+  int out_L;              // stored row length of out
+  int out_stride;         // 1, or f for transposed-conv phases
+  int n_phase;            // 1, or f
+  int up_f, up_P;         // transposed conv: phase r -> shift (r+P)/f, out_offset r
+  int tanh_out;
+  float slope;
+};
+
+// cpt = output channels per thread (tile is 16*cpt channels x 128 time positions, 256 threads).
+int conv_f32_pick_cpt(int Cout);
+cudaError_t conv_f32_launch(const ConvParams& p, int batch, int cpt, cudaStream_t stream);
+
+// ---- PQMF (pqmf.cu) ----------------------------------------------------------------------------
+cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int bands, int taps,
+                                  int64_t Ts, float* y, cudaStream_t stream);
+cudaError_t pqmf_analysis_launch(const float* x, const float* H, int batch, int bands, int taps,
+                                 int64_t T, float* y, cudaStream_t stream);
+
+}  // namespace ttsb

@@ -1,0 +1,123 @@
+"""MelganGenerator: the reference's Python surface over the B200 CUDA plan.
+
+Surface kept (TTS/vocoder/models/melgan_generator.py:8-97): constructor
+arguments, ``layers`` (an ``nn.Sequential`` with the reference's indices and state-dict keys),
+``inference_padding``, ``forward``, ``inference``, ``remove_weight_norm``, plus normal
+``nn.Module`` behaviour (``load_state_dict``, ``.cuda()``, ``.eval()``, ``.parameters()``).
+
+What runs where:
+  * ``inference(c)`` and eval-mode ``forward(c)`` -> hand-written sm_100a kernels through
+    include/tts_b200.h (tts_b200/engine.py).  CUDA only; raises on CPU-resident modules.
+  * training-mode ``forward(c)`` -> ``self.layers`` with autograd (training is out of scope;
+    the trainer needs gradients, train_vocoder.py:111).
+New attribute: ``precision`` = "fp32" (max-abs <= 1e-5 vs reference) or "bf16" (tcgen05, SNR >= 40 dB).
+"""
+import threading
+
+import torch
+from torch import nn
+from torch.nn.utils import weight_norm
+
+from ..layers.melgan import ResidualStack
+from ... import _lib
+
+
+class MelganGenerator(nn.Module):
+    def __init__(self,
+                 in_channels=80,
+                 out_channels=1,
+                 proj_kernel=7,
+                 base_channels=512,
+                 upsample_factors=(8, 8, 2, 2),
+                 res_kernel=3,
+                 num_res_blocks=3):
+        super().__init__()
+        assert (proj_kernel - 1) % 2 == 0, " [!] proj_kernel should be an odd number."
+        self.in_channels = in_channels
+        self.out_channels = out_channels
+        self.proj_kernel = proj_kernel
+        self.base_channels = base_channels
+        self.upsample_factors = tuple(int(f) for f in upsample_factors)
+        self.res_kernel = res_kernel
+        self.num_res_blocks = num_res_blocks
+        self.inference_padding = 2
+        self.precision = "fp32"
+
+        edge = (proj_kernel - 1) // 2
+        seq = [nn.ReflectionPad1d(edge),
+               weight_norm(nn.Conv1d(in_channels, base_channels, kernel_size=proj_kernel, stride=1, bias=True))]
+        width = base_channels
+        for f in self.upsample_factors:
+            odd = f % 2
+            seq.append(nn.LeakyReLU(0.2))
+            seq.append(weight_norm(nn.ConvTranspose1d(width, width // 2, 2 * f, stride=f, padding=f // 2 + odd,
+                                                      output_padding=odd, bias=True)))
+            seq.append(ResidualStack(channels=width // 2, num_res_blocks=num_res_blocks, kernel_size=res_kernel))
+            width //= 2
+        seq += [nn.LeakyReLU(0.2),
+                nn.ReflectionPad1d(edge),
+                weight_norm(nn.Conv1d(width, out_channels, proj_kernel, stride=1, bias=True)),
+                nn.Tanh()]
+        self.layers = nn.Sequential(*seq)
+
+        self._engine = None
+        self._engine_sig = None
+        self._engine_lock = threading.Lock()
+        self._frozen = False
+
+    # ------------------------------------------------------------------ plan management
+    def _signature(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    def _get_engine(self):
+        dev = self.layers[1].bias.device
+        if dev.type != "cuda":
+            raise RuntimeError(
+                "tts_b200: this generator runs on CUDA (sm_100a) only — move it with .cuda() first. "
+                "There is no CPU fallback for inference.")
+        if self._engine is not None and self._frozen:
+            return self._engine
+        sig = (dev, self._signature())
+        with self._engine_lock:
+            if self._engine is None or self._engine_sig != sig:
+                from ...engine import GeneratorEngine
+                if self._engine is not None:
+                    self._engine.close()
+                self._engine = GeneratorEngine(self, dev)
+                self._engine_sig = sig
+        return self._engine
+
+    def freeze(self, frozen=True):
+        """Skip the per-call weight-change check (latency path). Call after the weights are final."""
+        self._frozen = frozen
+        return self
+
+    def _apply(self, fn, *a, **kw):  # .cuda()/.to()/.float() invalidate the plan
+        self._engine_sig = None
+        self._frozen = False
+        return super()._apply(fn, *a, **kw)
+
+    def _run(self, c, pad, skip_pqmf, tap_layers=None, profile=None):
+        eng = self._get_engine()
+        c = c.detach().to(device=eng.device, dtype=torch.float32)
+        prec = _lib.PRECISIONS[self.precision]
+        return eng.forward(c, int(pad), prec, skip_pqmf=skip_pqmf, tap_layers=tap_layers, profile=profile)
+
+    # ------------------------------------------------------------------ reference surface
+    def forward(self, c):
+        if self.training:
+            return self.layers(c)
+        return self._run(c, 0, True)
+
+    def inference(self, c):
+        return self._run(c, self.inference_padding, True)
+
+    def inference_with_taps(self, c, tap_layers):
+        """inference() that also returns {layers[i] index: output} for per-layer parity tests."""
+        return self._run(c, self.inference_padding, True, tap_layers=list(tap_layers))
+
+    def remove_weight_norm(self):
+        for m in self.modules():
+            if isinstance(m, (nn.Conv1d, nn.ConvTranspose1d)) and hasattr(m, "weight_g"):
+                nn.utils.remove_weight_norm(m)
+        self._engine_sig = None
