@@ -210,3 +210,84 @@ def test_streams_and_threads():
     [t.join() for t in ts]
     for w, g_ in zip(want, got):
         assert torch.equal(w, g_)
+
+
+# ------------------------------------------------------------------------------------------------
+# BF16 operands / fp32 accumulate on tcgen05.
+#   (1) vs oracle/bf16_emulation.py (same rounding points on the CPU): must agree to accumulation-order
+#       noise, per layer and end to end — this is the kernel-correctness check;
+#   (2) vs the fp32 reference on the reference's own default-init weights: SNR >= 40 dB (north_star).
+# ------------------------------------------------------------------------------------------------
+BF16_SNR = 40.0
+NORTH_STAR = 3   # CASES[:3] are the BASELINE.json models (MelGAN cfg1, MB-MelGAN defaults): the 40 dB bar applies
+
+
+def default_init(cls, kw):
+    """Reference default init under the reference's training seed (TTS/utils/training.py:8)."""
+    torch.manual_seed(54321)
+    m = CLS[cls](**kw)
+    m.remove_weight_norm()
+    sd = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    return m.cuda().eval(), getattr(GeneratorSpec, cls)(**kw), sd
+
+
+@pytest.mark.parametrize("case", range(len(CASES)))
+@pytest.mark.parametrize("init", ["oracle_random", "reference_default"])
+def test_bf16_end_to_end_and_per_layer(case, init):
+    cls, kw, B, T, p = CASES[case]
+    from oracle.bf16_emulation import generator_inference_bf16
+    m, spec, sd = build(cls, kw, seed=11) if init == "oracle_random" else default_init(cls, kw)
+    m.inference_padding = p
+    m.precision = "bf16"
+    g = torch.Generator().manual_seed(5)
+    mel = torch.randn(B, spec.in_channels, T, generator=g)
+    taps_emu = {}
+    emu = generator_inference_bf16(spec, sd, mel, p, taps=taps_emu)
+    ref = generator_inference(spec, sd, mel, p)
+    layers = [1] + [spec.idx_upsample(s) for s in range(spec.n_stages)] + \
+             [spec.idx_stack(s) for s in range(spec.n_stages)] + [spec.idx_head() + 1]
+    out, taps = m.inference_with_taps(mel, layers)
+    torch.cuda.synchronize()
+    assert out.shape == ref.shape and out.dtype == torch.float32
+    # BF16 rounding is the error source, so the yardstick is the emulation's own distance to fp32:
+    # the kernel may differ from the emulation only by accumulation-order rounding flips, i.e. by
+    # less than that inherent error, and must sit at the same distance from the fp32 reference.
+    inherent = snr_db(ref, emu)
+    for i in layers:
+        s = snr_db(taps_emu[i], taps[i].cpu())
+        assert s >= min(45.0, inherent), (i, s)      # taps are read back from stored bf16 (one more rounding)
+    got = snr_db(ref, out.cpu())
+    assert snr_db(emu, out.cpu()) >= inherent - 3.0, (snr_db(emu, out.cpu()), inherent)
+    assert got >= inherent - 1.5, (got, inherent)
+    if init == "reference_default" and case < NORTH_STAR:
+        assert got >= BF16_SNR, got
+
+
+def test_bf16_full_size_cfg2_and_golden(golden):
+    g = golden("mb_cfg2_item")
+    m, spec, sd = default_init("multiband", {})
+    m.precision = "bf16"
+    torch.manual_seed(1234)
+    mel = torch.randn(1, 80, 862)
+    out = m.inference(mel).cpu()
+    assert tuple(out.shape) == tuple(g["out_shape"])
+    ref_sub = torch.from_numpy(g["out"])                     # output of the unmodified reference
+    assert snr_db(ref_sub, out[..., ::int(g["sub"])]) >= BF16_SNR
+    # batch of 16: items independent and deterministic
+    melb = torch.randn(16, 80, 862, generator=torch.Generator().manual_seed(9)).cuda()
+    a = m.inference(melb)
+    assert bool(torch.isfinite(a).all())
+    assert torch.equal(m.inference(melb[3:4])[0], a[3])
+    assert torch.equal(m.inference(melb), a)
+    m.precision = "fp32"
+    f = m.inference(melb)
+    assert snr_db(f.cpu(), a.cpu()) >= BF16_SNR
+
+
+def test_bf16_melgan_cfg1_golden(golden):
+    g = golden("melgan_cfg1")
+    m, spec, sd = default_init("melgan", {})
+    m.precision = "bf16"
+    torch.manual_seed(1234)
+    out = m.inference(torch.randn(1, 80, 200)).cpu().numpy()
+    assert snr_db(torch.from_numpy(g["out"]), torch.from_numpy(out)) >= BF16_SNR

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libtts_b200.so")
-SOURCES = ["vocoder.cu", "conv_f32.cu", "pqmf.cu"]
+SOURCES = ["vocoder.cu", "conv_f32.cu", "pqmf.cu", "conv_bf16_tc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
@@ -33,7 +33,7 @@ def needs_build():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h", ".inl"))]
     deps.append(os.path.join(HERE, "..", "include", "tts_b200.h"))
     return any(os.path.getmtime(d) > t for d in deps)
 

@@ -1,0 +1,307 @@
+// BF16 implicit-GEMM 1-D convolution on tcgen05 / TMEM for the vocoder's dense contractions:
+// k7 projection and head, ConvTranspose1d upsampling (as two phase classes of 2-tap convs), the
+// dilated k3 residual conv and the fused (1x1 conv + 1x1 shortcut) of ResidualStack
+// (TTS/vocoder/models/melgan_generator.py:29-78, TTS/vocoder/layers/melgan.py:13-38).
+//
+// GEMM view per CTA: D[128 time rows, ncols <= 256 out-channels] += A[128, K] * W[ncols, K]^T with
+// K = sources x taps x C_in.  The activation tile (128 + tap span rows, all channels) is brought in
+// ONCE by cp.async.bulk straight into the canonical UMMA layout; every tap of a (dilated) conv is
+// the same tile read at a different start row, i.e. only the A descriptor's start address
+// changes (verified on hardware by tests/cuda/umma_probe.cu).  Weights stream through a 3-stage
+// bulk-copy ring.  fp32 accumulators live in TMEM; the epilogue warps read them back with
+// tcgen05.ld, add bias, apply LeakyReLU / tanh and write the next layer's operand layout.
+//
+// Warp roles (192 threads): warp 0 = copy producer + TMEM owner, warp 1 = MMA issuer (one
+// thread), warps 2..5 = LeakyReLU prologue in shared memory + epilogue (one TMEM lane quarter each).
+#include "common.cuh"
+#include "tc_common.cuh"
+#include "tc_conv.cuh"
+
+namespace ttsb {
+
+using namespace tc;
+
+namespace {
+
+constexpr int NT = 192;
+
+__device__ __forceinline__ float lrelu_f(float v, float s) { return v >= 0.f ? v : v * s; }
+
+__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t u, float slope) {
+  const float lo = lrelu_f(__uint_as_float(u << 16), slope);
+  const float hi = lrelu_f(__uint_as_float(u & 0xFFFF0000u), slope);
+  return pack_bf16x2(lo, hi);
+}
+
+__global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcConvParams p, const int w_stage_bytes,
+                                                      const int nst) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bar_a, bar_a_ready, bar_d, bar_full[TC_STAGES], bar_empty[TC_STAGES];
+  __shared__ uint32_t tmem_base_s;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int t0 = blockIdx.x * TC_TILE_M;
+  const TcGroup& G = p.grp[blockIdx.y];
+  const int b = blockIdx.z;
+  const int ncols = G.ncols;
+
+  const uint32_t a_bytes0 = (uint32_t)p.src[0].planes * p.src[0].rows * 16;
+  const uint32_t a_bytes1 = p.nsrc > 1 ? (uint32_t)p.src[1].planes * p.src[1].rows * 16 : 0;
+  uint8_t* sA0 = smem;
+  uint8_t* sA1 = smem + a_bytes0;
+  uint8_t* sW = smem + a_bytes0 + a_bytes1;
+
+  uint32_t tcols = 32;
+  while (tcols < (uint32_t)ncols) tcols <<= 1;
+  const bool need_lrelu = p.src[0].lrelu || (p.nsrc > 1 && p.src[1].lrelu);
+
+  if (tid == 0) {
+    mbar_init(&bar_a, 1);
+    mbar_init(&bar_a_ready, 128);
+    mbar_init(&bar_d, 1);
+    for (int s = 0; s < nst; ++s) {
+      mbar_init(&bar_full[s], 1);
+      mbar_init(&bar_empty[s], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc(&tmem_base_s, tcols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = tmem_base_s;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---- activation tile(s): one bulk copy per 8-channel plane
+      mbar_expect_tx(&bar_a, a_bytes0 + a_bytes1);
+      for (int s = 0; s < p.nsrc; ++s) {
+        const TcSrc& S = p.src[s];
+        const __nv_bfloat16* gx = S.x + (int64_t)b * S.batch_stride + (int64_t)(S.row_base + t0) * 8;
+        uint8_t* dst = s ? sA1 : sA0;
+        const uint32_t plane_bytes = (uint32_t)S.rows * 16;
+        for (int pl = 0; pl < S.planes; ++pl)
+          bulk_g2s(dst + (size_t)pl * plane_bytes, gx + (int64_t)pl * S.plane_rows * 8, plane_bytes, &bar_a);
+      }
+      // ---- weight ring
+      int it = 0;
+      const __nv_bfloat16* gw = G.w;
+      for (int s = 0; s < p.nsrc; ++s) {
+        const int cp = p.src[s].planes * 8;
+        for (int j = 0; j < p.src[s].taps; ++j)
+          for (int c0 = 0; c0 < cp; c0 += TC_KB, ++it) {
+            const int kb = min(TC_KB, cp - c0);
+            const int st = it % nst;
+            const uint32_t ph = (it / nst) & 1;
+            mbar_wait(&bar_empty[st], ph ^ 1);
+            const uint32_t bytes = (uint32_t)(kb / 8) * ncols * 16;
+            mbar_expect_tx(&bar_full[st], bytes);
+            bulk_g2s(sW + (size_t)st * w_stage_bytes, gw, bytes, &bar_full[st]);
+            gw += (int64_t)kb * ncols;
+          }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      if (need_lrelu) mbar_wait(&bar_a_ready, 0); else mbar_wait(&bar_a, 0);
+      tc_fence_after();
+      const uint32_t idesc = make_idesc_bf16(TC_TILE_M, ncols);
+      const uint32_t lbo_b = (uint32_t)ncols * 16;
+      int it = 0;
+      uint32_t acc = 0;
+      for (int s = 0; s < p.nsrc; ++s) {
+        const TcSrc& S = p.src[s];
+        const int cp = S.planes * 8;
+        const uint32_t lbo_a = (uint32_t)S.rows * 16;
+        const uint32_t a_base = smem_u32(s ? sA1 : sA0);
+        for (int j = 0; j < S.taps; ++j) {
+          const uint32_t a_tap = a_base + (uint32_t)(S.tap_row[j] + G.tap_shift) * 16;
+          for (int c0 = 0; c0 < cp; c0 += TC_KB, ++it) {
+            const int kb = min(TC_KB, cp - c0);
+            const int st = it % nst;
+            const uint32_t ph = (it / nst) & 1;
+            mbar_wait(&bar_full[st], ph);
+            tc_fence_after();
+            const uint32_t w_base = smem_u32(sW + (size_t)st * w_stage_bytes);
+            for (int kk = 0; kk < kb / 16; ++kk) {
+              const uint64_t ad = make_desc(a_tap + (uint32_t)((c0 >> 3) + 2 * kk) * lbo_a, lbo_a, 128);
+              const uint64_t bd = make_desc(w_base + (uint32_t)(2 * kk) * lbo_b, lbo_b, 128);
+              umma_bf16(tbase, ad, bd, idesc, acc);
+              acc = 1;
+            }
+            umma_commit(&bar_empty[st]);  // frees the stage once these MMAs have read it
+          }
+        }
+      }
+      umma_commit(&bar_d);
+    }
+  } else {
+    // ---- warps 2..5: optional LeakyReLU over the staged tile, then the epilogue
+    const int et = tid - 64;
+    if (need_lrelu) {
+      mbar_wait(&bar_a, 0);
+      for (int s = 0; s < p.nsrc; ++s) {
+        if (!p.src[s].lrelu) continue;
+        uint4* v = reinterpret_cast<uint4*>(s ? sA1 : sA0);
+        const int nvec = (s ? a_bytes1 : a_bytes0) / 16;
+        for (int e = et; e < nvec; e += 128) {
+          uint4 u = v[e];
+          u.x = lrelu_bf16x2(u.x, p.slope); u.y = lrelu_bf16x2(u.y, p.slope);
+          u.z = lrelu_bf16x2(u.z, p.slope); u.w = lrelu_bf16x2(u.w, p.slope);
+          v[e] = u;
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(&bar_a_ready);
+    }
+    mbar_wait(&bar_d, 0);
+    tc_fence_after();
+    const int q4 = warp & 3;                 // TMEM lane quarter this warp may read
+    const int m = q4 * 32 + lane;
+    const int t = t0 + m;
+    const bool row_ok = t < p.Lt;
+    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
+    for (int c = 0; c < ncols; c += 16) {
+      float v[16];
+      tmem_ld16(trow + c, v);
+      const int flat = G.ch_first + c;
+      const int r = G.phase_first + flat / p.cout_pad;
+      const int ch = flat % p.cout_pad;
+      const int tau = t * p.up_f + r;
+      if (!row_ok || tau >= p.out_L) continue;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] += __ldg(G.bias + c + i);
+      if (p.out_mode == 0) {
+        if (p.out_lrelu) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = lrelu_f(v[i], p.slope);
+        }
+        uint4 lo, hi;
+        lo.x = pack_bf16x2(v[0], v[1]);   lo.y = pack_bf16x2(v[2], v[3]);
+        lo.z = pack_bf16x2(v[4], v[5]);   lo.w = pack_bf16x2(v[6], v[7]);
+        hi.x = pack_bf16x2(v[8], v[9]);   hi.y = pack_bf16x2(v[10], v[11]);
+        hi.z = pack_bf16x2(v[12], v[13]); hi.w = pack_bf16x2(v[14], v[15]);
+        __nv_bfloat16* ob = p.out_c + (int64_t)b * p.out_batch_stride;
+        const int64_t pl0 = (int64_t)(ch >> 3) * p.out_plane_rows;
+        const int64_t pl1 = pl0 + p.out_plane_rows;
+        auto put = [&](int row) {
+          *reinterpret_cast<uint4*>(ob + (pl0 + row) * 8) = lo;
+          *reinterpret_cast<uint4*>(ob + (pl1 + row) * 8) = hi;
+        };
+        put(p.out_halo + tau);
+        if (p.margin == 1) {           // halo rows mirror the interior (ReflectionPad1d of the consumer)
+          if (tau >= 1 && tau <= p.out_halo) put(p.out_halo - tau);
+          const int back = p.out_L - 1 - tau;
+          if (back >= 1 && back <= p.out_halo) put(p.out_halo + p.out_L - 1 + back);
+        } else if (p.margin == 2) {    // zero rows either side (transposed conv of the consumer)
+          const uint4 z = make_uint4(0, 0, 0, 0);
+          if (tau == 0) {
+            *reinterpret_cast<uint4*>(ob + (pl0 + p.out_halo - 1) * 8) = z;
+            *reinterpret_cast<uint4*>(ob + (pl1 + p.out_halo - 1) * 8) = z;
+          }
+          if (tau == p.out_L - 1) {
+            *reinterpret_cast<uint4*>(ob + (pl0 + p.out_halo + p.out_L) * 8) = z;
+            *reinterpret_cast<uint4*>(ob + (pl1 + p.out_halo + p.out_L) * 8) = z;
+          }
+        }
+      } else {
+        float* of = p.out_f + ((int64_t)b * p.cout_real + ch) * p.out_L + tau;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (ch + i < p.cout_real) of[(int64_t)i * p.out_L] = tanhf(v[i]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tbase, tcols);
+}
+
+// ---- layout helpers --------------------------------------------------------------------------------
+__global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int pad, __nv_bfloat16* __restrict__ out,
+                                int planes, int plane_rows, int halo) {
+  // one thread per (plane row, plane); row index covers halo margins too (reflect of the padded signal)
+  const int L = T + 2 * pad;
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pl = blockIdx.y, b = blockIdx.z;
+  if (row >= plane_rows) return;
+  int t = row - halo;                       // position in the replicate-padded signal
+  bool ok = t > -L && t < 2 * L - 1;        // mirror only defined within one reflection
+  if (t < 0) t = -t;
+  if (t >= L) t = 2 * (L - 1) - t;
+  int src = t - pad;
+  src = src < 0 ? 0 : (src >= T ? T - 1 : src);
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float a = 0.f, c = 0.f;
+    const int c0 = pl * 8 + 2 * i;
+    if (ok && c0 < C) a = mel[((int64_t)b * C + c0) * T + src];
+    if (ok && c0 + 1 < C) c = mel[((int64_t)b * C + c0 + 1) * T + src];
+    w[i] = pack_bf16x2(a, c);
+  }
+  *reinterpret_cast<uint4*>(out + (((int64_t)b * planes + pl) * plane_rows + row) * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+__global__ void untile_kernel(const __nv_bfloat16* __restrict__ x, int C, int64_t L, int planes, int plane_rows,
+                              int halo, int undo_lrelu, float slope, float* __restrict__ out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = blockIdx.y, b = blockIdx.z;
+  if (t >= L) return;
+  float v = __bfloat162float(x[(((int64_t)b * planes + (c >> 3)) * plane_rows + halo + t) * 8 + (c & 7)]);
+  if (undo_lrelu && v < 0.f) v /= slope;
+  out[((int64_t)b * C + c) * L + t] = v;
+}
+
+}  // namespace
+
+namespace {
+constexpr size_t SMEM_MAX = 227 * 1024 - 1024;  // static barriers live in the same 227 KB
+struct SmemPlan { size_t a_bytes; int w_stage_bytes, nst; };
+SmemPlan smem_plan(const TcConvParams& p) {
+  SmemPlan s{};
+  s.a_bytes = (size_t)p.src[0].planes * p.src[0].rows * 16;
+  if (p.nsrc > 1) s.a_bytes += (size_t)p.src[1].planes * p.src[1].rows * 16;
+  int nmax = 0;
+  for (int g = 0; g < p.ngroups; ++g) nmax = nmax > p.grp[g].ncols ? nmax : p.grp[g].ncols;
+  s.w_stage_bytes = (TC_KB / 8) * nmax * 16;
+  s.nst = TC_STAGES;
+  while (s.nst > 2 && s.a_bytes + (size_t)s.nst * s.w_stage_bytes > SMEM_MAX) --s.nst;
+  return s;
+}
+}  // namespace
+
+// bytes of dynamic shared memory of the launch (deepest weight ring, 3 down to 2 stages, that fits)
+size_t tc_conv_smem_bytes(const TcConvParams& p) {
+  const SmemPlan s = smem_plan(p);
+  return s.a_bytes + (size_t)s.nst * s.w_stage_bytes;
+}
+
+cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream) {
+  {  // per-device attribute; cheap enough to set on every launch
+    cudaError_t e = cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    if (e != cudaSuccess) return e;
+  }
+  const SmemPlan sp = smem_plan(p);
+  const size_t smem = sp.a_bytes + (size_t)sp.nst * sp.w_stage_bytes;
+  if (smem > SMEM_MAX) return cudaErrorInvalidConfiguration;
+  const dim3 grid(ceil_div(p.Lt, TC_TILE_M), p.ngroups, batch);
+  tc_conv_kernel<<<grid, NT, smem, stream>>>(p, sp.w_stage_bytes, sp.nst);
+  return cudaGetLastError();
+}
+
+cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out, int planes,
+                               int plane_rows, int halo, cudaStream_t stream) {
+  const dim3 grid(ceil_div(plane_rows, 128), planes, batch);
+  prep_mel_kernel<<<grid, 128, 0, stream>>>(mel, C, T, pad, out, planes, plane_rows, halo);
+  return cudaGetLastError();
+}
+
+cudaError_t tc_untile_launch(const __nv_bfloat16* x, int batch, int C, int64_t L, int planes, int plane_rows, int halo,
+                             int undo_lrelu, float slope, float* out, cudaStream_t stream) {
+  const dim3 grid(ceil_div(L, 256), C, batch);
+  untile_kernel<<<grid, 256, 0, stream>>>(x, C, L, planes, plane_rows, halo, undo_lrelu, slope, out);
+  return cudaGetLastError();
+}
+
+}  // namespace ttsb

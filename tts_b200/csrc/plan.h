@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "tc_conv.cuh"
 
 namespace ttsb {
 
@@ -15,7 +16,19 @@ struct ConvF32 {
   size_t b_off = 0;  // [CoutPad]
 };
 
+// BF16 weights of one conv for the tcgen05 kernel: per column group, [src][tap][Cin_pad/8][ncols][8].
+struct TcGroupPlan {
+  size_t w_off = 0;     // bf16-element offset into the plan's bf16 blob
+  size_t bias_off = 0;  // float offset into the fp32 blob, [ncols]
+  int ncols = 0, tap_shift = 0, phase_first = 0, ch_first = 0;
+};
+struct TcLayer {
+  int cin_pad = 0, cout_pad = 0, cout = 0, up_f = 1;
+  std::vector<TcGroupPlan> groups;
+};
+
 struct BlockPlan {
+  TcLayer tc_conv1, tc_conv2s;  // BF16: dilated k3; fused (1x1 on lrelu(h)) + (1x1 shortcut on x)
   int dilation = 1;
   ConvF32 conv1;     // dilated k3                                   melgan.py:20-24
   ConvF32 conv2;     // 1x1 after the second LeakyReLU               melgan.py:26-27
@@ -27,6 +40,7 @@ struct StagePlan {
   int f = 1, P = 0, Cin = 0, Cout = 0;
   int layer_up = 0, layer_stack = 0;  // reference layers[] indices
   ConvF32 up;                         // ConvTranspose1d as f two-tap phases
+  TcLayer tc_up;                      // BF16: two phase classes (q = 0 / 1), 2 taps each
   std::vector<BlockPlan> blocks;
 };
 
@@ -47,6 +61,10 @@ struct ttsb200_plan {
   float* blob = nullptr;  // all fp32 weights
   size_t blob_floats = 0;
   ttsb::ConvF32 proj, head;
+  ttsb::TcLayer tc_proj, tc_head;
+  __nv_bfloat16* blob16 = nullptr;  // all BF16 weights (UMMA canonical K-major layout)
+  size_t blob16_elems = 0;
+  int halo = 8;                     // margin rows either side of every canonical activation plane
   std::vector<ttsb::StagePlan> stages;
   size_t pqmf_G_off = 0;  // [N][taps+1]
   int hop_generator = 1;  // prod(upsample_factors)

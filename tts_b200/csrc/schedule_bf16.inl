@@ -1,0 +1,332 @@
+// BF16 / tcgen05 half of vocoder.cu (included inside its anonymous namespace): weight packing into
+// the UMMA canonical layout and the launch schedule of generator.inference().
+//
+// Every intermediate is a "canonical" bf16 tensor [B][C_pad/8][rows][8], rows = roundup(L,128) + 2*halo,
+// whose halo rows are filled by the PRODUCER with what its single consumer's padding rule needs
+// (mirror rows for ReflectionPad1d, zero rows for the transposed conv), and stored already
+// LeakyReLU-activated when the consumer only ever reads lrelu(x).  So every kernel's loads are
+// plain contiguous bulk copies and no pad / activation kernel exists.
+
+struct Bf16Builder {
+  std::vector<__nv_bfloat16> data;
+  size_t alloc(size_t n) {
+    size_t off = (data.size() + 63) / 64 * 64;
+    data.resize(off + n, __float2bfloat16(0.f));
+    return off;
+  }
+};
+
+struct PhaseClass {
+  int phase_first, n_phases, tap_shift;
+};
+
+inline int pad16(int c) { return (int)round_up(c, 16); }
+
+// wfun(src, tap, ci, phase, co) / bfun(co): reference weights; channels beyond the real counts are zero.
+template <class WF, class BF>
+int pack_tc_layer(Bf16Builder& b16, BlobBuilder& bb, TcLayer& L, int nsrc, const int* taps, const int* cin, int cout,
+                  int up_f, const std::vector<PhaseClass>& classes, WF wfun, BF bfun) {
+  L.cin_pad = pad16(cin[0]);
+  L.cout_pad = pad16(cout);
+  L.cout = cout;
+  L.up_f = up_f;
+  L.groups.clear();
+  for (const PhaseClass& pc : classes) {
+    const int flat = pc.n_phases * L.cout_pad;
+    int ncols = 16;
+    for (int n = 256; n >= 16; n -= 16)
+      if (flat % n == 0) { ncols = n; break; }
+    for (int col0 = 0; col0 < flat; col0 += ncols) {
+      TcGroupPlan g;
+      g.ncols = ncols;
+      g.tap_shift = pc.tap_shift;
+      g.phase_first = pc.phase_first + col0 / L.cout_pad;
+      g.ch_first = col0 % L.cout_pad;
+      size_t total = 0;
+      for (int s = 0; s < nsrc; ++s) total += (size_t)taps[s] * pad16(cin[s]) * ncols;
+      g.w_off = b16.alloc(total);
+      g.bias_off = bb.alloc(ncols);
+      size_t base = g.w_off;
+      for (int s = 0; s < nsrc; ++s) {
+        const int cp = pad16(cin[s]);
+        for (int j = 0; j < taps[s]; ++j) {
+          for (int ci = 0; ci < cin[s]; ++ci)
+            for (int col = 0; col < ncols; ++col) {
+              const int fl = g.ch_first + col;
+              const int ph = g.phase_first + fl / L.cout_pad, co = fl % L.cout_pad;
+              if (co >= cout) continue;
+              b16.data[base + ((size_t)(ci >> 3) * ncols + col) * 8 + (ci & 7)] =
+                  __float2bfloat16(wfun(s, j, ci, ph, co));
+            }
+          base += (size_t)cp * ncols;
+        }
+      }
+      for (int col = 0; col < ncols; ++col) {
+        const int co = (g.ch_first + col) % L.cout_pad;
+        bb.data[g.bias_off + col] = co < cout ? bfun(co) : 0.f;
+      }
+      L.groups.push_back(g);
+    }
+  }
+  if ((int)L.groups.size() > TC_MAX_GROUPS) return fail(TTSB200_ERR_INVALID, "layer needs too many column groups");
+  return 0;
+}
+
+// tensors[] in ttsb200_plan_create order; fills plan->tc_* and uploads plan->blob16 later.
+int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, Bf16Builder& b16) {
+  const ttsb200_generator_config& cfg = plan->cfg;
+  const std::vector<PhaseClass> plain{{0, 1, 0}};
+  int ti = 0;
+  int max_d = (cfg.proj_kernel - 1) / 2;
+  {
+    const float *w = tensors[ti], *b = tensors[ti + 1];
+    const int taps[1] = {cfg.proj_kernel}, cin[1] = {cfg.in_channels};
+    const int Cin = cfg.in_channels, k = cfg.proj_kernel;
+    if (int rc = pack_tc_layer(b16, bb, plan->tc_proj, 1, taps, cin, cfg.base_channels, 1, plain,
+                               [&](int, int j, int ci, int, int co) { return w[((size_t)co * Cin + ci) * k + j]; },
+                               [&](int co) { return b[co]; }))
+      return rc;
+    ti += 2;
+  }
+  int clast = cfg.base_channels;
+  for (int s = 0; s < cfg.n_stages; ++s) {
+    StagePlan& sp = plan->stages[s];
+    {
+      const float *w = tensors[ti], *b = tensors[ti + 1];
+      const int f = sp.f, P = sp.P, Cout = sp.Cout;
+      // phases with (r + P) / f == 0 read x[m], x[m-1]; the rest read x[m+1], x[m]
+      const int n0 = std::max(0, std::min(f, f - P));
+      std::vector<PhaseClass> classes;
+      if (n0 > 0) classes.push_back({0, n0, 0});
+      if (n0 < f) classes.push_back({n0, f - n0, 1});
+      const int taps[1] = {2}, cin[1] = {sp.Cin};
+      if (int rc = pack_tc_layer(b16, bb, sp.tc_up, 1, taps, cin, Cout, f, classes,
+                                 [&](int, int j, int ci, int ph, int co) {
+                                   return w[((size_t)ci * Cout + co) * (2 * f) + (ph + P) % f + f * j];
+                                 },
+                                 [&](int co) { return b[co]; }))
+        return rc;
+      ti += 2;
+    }
+    const int C = sp.Cout, k = cfg.res_kernel, nb = cfg.num_res_blocks;
+    const int ti_blocks = ti, ti_short = ti + 4 * nb;
+    for (int bi = 0; bi < nb; ++bi) {
+      BlockPlan& bp = sp.blocks[bi];
+      max_d = std::max(max_d, (k - 1) / 2 * bp.dilation);
+      const float *w1 = tensors[ti_blocks + 4 * bi], *b1 = tensors[ti_blocks + 4 * bi + 1];
+      const float *w2 = tensors[ti_blocks + 4 * bi + 2], *b2 = tensors[ti_blocks + 4 * bi + 3];
+      const float *ws = tensors[ti_short + 2 * bi], *bs = tensors[ti_short + 2 * bi + 1];
+      {
+        const int taps[1] = {k}, cin[1] = {C};
+        if (int rc = pack_tc_layer(b16, bb, bp.tc_conv1, 1, taps, cin, C, 1, plain,
+                                   [&](int, int j, int ci, int, int co) { return w1[((size_t)co * C + ci) * k + j]; },
+                                   [&](int co) { return b1[co]; }))
+          return rc;
+      }
+      {
+        const int taps[2] = {1, 1}, cin[2] = {C, C};
+        if (int rc = pack_tc_layer(b16, bb, bp.tc_conv2s, 2, taps, cin, C, 1, plain,
+                                   [&](int src, int, int ci, int, int co) {
+                                     return (src == 0 ? w2 : ws)[(size_t)co * C + ci];
+                                   },
+                                   [&](int co) { return b2[co] + bs[co]; }))
+          return rc;
+      }
+    }
+    ti += 6 * nb;
+    clast = C;
+  }
+  {
+    const float *w = tensors[ti], *b = tensors[ti + 1];
+    const int taps[1] = {cfg.proj_kernel}, cin[1] = {clast};
+    const int k = cfg.proj_kernel;
+    if (int rc = pack_tc_layer(b16, bb, plan->tc_head, 1, taps, cin, cfg.out_channels, 1, plain,
+                               [&](int, int j, int ci, int, int co) { return w[((size_t)co * clast + ci) * k + j]; },
+                               [&](int co) { return b[co]; }))
+      return rc;
+  }
+  plan->halo = (int)round_up(std::max(max_d, 1), 8);
+  return 0;
+}
+
+struct CanonDims {
+  int planes, rows;
+  size_t elems;  // per batch item
+};
+inline CanonDims canon_dims(const ttsb200_plan* plan, int C, int64_t L) {
+  CanonDims d;
+  d.planes = pad16(C) / 8;
+  d.rows = (int)round_up(L, TC_TILE_M) + 2 * plan->halo;
+  d.elems = (size_t)d.planes * d.rows * 8;
+  return d;
+}
+
+struct Bf16Workspace {
+  size_t mel_elems, buf_elems, head_floats, total_bytes;
+};
+Bf16Workspace bf16_workspace(const ttsb200_plan* plan, int B, const Shape& sh) {
+  const ttsb200_generator_config& cfg = plan->cfg;
+  Bf16Workspace w{};
+  w.mel_elems = (size_t)round_up((int64_t)B * canon_dims(plan, cfg.in_channels, sh.L0).elems, 128);
+  size_t mx = canon_dims(plan, cfg.base_channels, sh.L0).elems;
+  for (size_t s = 0; s < plan->stages.size(); ++s)
+    mx = std::max(mx, canon_dims(plan, plan->stages[s].Cout, sh.L[s]).elems);
+  w.buf_elems = (size_t)round_up((int64_t)B * mx, 128);
+  w.head_floats = (size_t)round_up((int64_t)B * cfg.out_channels * sh.L.back(), 64);
+  w.total_bytes = (w.mel_elems + 3 * w.buf_elems) * sizeof(__nv_bfloat16) + w.head_floats * sizeof(float);
+  return w;
+}
+
+int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
+  const ttsb200_generator_config& cfg = plan->cfg;
+  if (cfg.proj_kernel > TC_MAX_TAPS || cfg.res_kernel > TC_MAX_TAPS)
+    return fail(TTSB200_ERR_INVALID, "BF16 path supports kernel sizes up to 7");
+  const Shape sh = shapes_for(plan, a->frames, a->pad);
+  if (int rc = check_lengths(plan, sh)) return rc;
+  const int B = a->batch, halo = plan->halo;
+  const Bf16Workspace wsz = bf16_workspace(plan, B, sh);
+  if (!a->workspace || a->workspace_bytes < wsz.total_bytes)
+    return fail(TTSB200_ERR_WORKSPACE, "workspace smaller than ttsb200_workspace_bytes()");
+  __nv_bfloat16* melc = static_cast<__nv_bfloat16*>(a->workspace);
+  __nv_bfloat16* cur = melc + wsz.mel_elems;
+  __nv_bfloat16* nxt = cur + wsz.buf_elems;
+  __nv_bfloat16* hbuf = nxt + wsz.buf_elems;
+  float* headf = reinterpret_cast<float*>(hbuf + wsz.buf_elems);
+  cudaStream_t st = static_cast<cudaStream_t>(a->stream);
+  Launcher ln{st, a->profile, B};
+  const float* Wf = plan->blob;
+  const __nv_bfloat16* Wh = plan->blob16;
+  const float slope = cfg.act_slope;
+  const int pp = (cfg.proj_kernel - 1) / 2;
+  const int S = cfg.n_stages, nb = cfg.num_res_blocks;
+
+  auto base = [&](const TcLayer& L, int64_t Lt) {
+    TcConvParams p{};
+    p.nsrc = 1;
+    p.ngroups = (int)L.groups.size();
+    for (int g = 0; g < p.ngroups; ++g) {
+      const TcGroupPlan& gp = L.groups[g];
+      p.grp[g] = TcGroup{Wh + gp.w_off, Wf + gp.bias_off, gp.ncols, gp.tap_shift, gp.phase_first, gp.ch_first};
+    }
+    p.Lt = (int)Lt; p.up_f = L.up_f; p.cout_pad = L.cout_pad; p.cout_real = L.cout; p.slope = slope;
+    return p;
+  };
+  auto src = [&](const __nv_bfloat16* x, int C, int64_t L, int taps, int step, int first, bool lrelu,
+                 int extra_hi = 0) {
+    const CanonDims d = canon_dims(plan, C, L);
+    TcSrc s{};
+    s.x = x; s.batch_stride = (int64_t)d.elems; s.planes = d.planes; s.plane_rows = d.rows;
+    const int lo = std::min(first, first + (taps - 1) * step);
+    const int hi = std::max(first, first + (taps - 1) * step) + extra_hi;   // extra_hi: room for the group shift
+    s.row_base = halo + lo; s.rows = TC_TILE_M + (hi - lo); s.taps = taps;
+    for (int j = 0; j < taps; ++j) s.tap_row[j] = first + j * step - lo;
+    s.lrelu = lrelu ? 1 : 0;
+    return s;
+  };
+  auto canon_out = [&](TcConvParams& p, __nv_bfloat16* out, int C, int64_t L, bool lrelu, int margin) {
+    const CanonDims d = canon_dims(plan, C, L);
+    p.out_mode = 0; p.out_c = out; p.out_batch_stride = (int64_t)d.elems; p.out_plane_rows = d.rows;
+    p.out_halo = halo; p.out_L = (int)L; p.out_lrelu = lrelu ? 1 : 0; p.margin = margin;
+  };
+  auto run = [&](const char* name, int layer, const TcConvParams& p, double macs, double io_elems) -> int {
+    if (tc_conv_smem_bytes(p) > 227 * 1024 - 1024)
+      return fail(TTSB200_ERR_INVALID, std::string(name) + ": tile does not fit shared memory on the BF16 path");
+    TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, st); }));
+    return 0;
+  };
+  auto tap = [&](int layer, const __nv_bfloat16* x, int C, int64_t L, bool undo) -> int {
+    for (int i = 0; i < a->n_taps; ++i)
+      if (a->tap_layers[i] == layer) {
+        const CanonDims d = canon_dims(plan, C, L);
+        TTSB_CUDA(tc_untile_launch(x, B, C, L, d.planes, d.rows, halo, undo, slope, a->tap_out[i], st));
+      }
+    return 0;
+  };
+
+  {  // mel -> canonical bf16 (replicate inference padding + reflect margin folded in)
+    const CanonDims d = canon_dims(plan, cfg.in_channels, sh.L0);
+    TTSB_CUDA(ln.run("bf16.prep.mel", 0, 0.0, 4.0 * B * cfg.in_channels * a->frames + 2.0 * B * d.elems, [&] {
+      return tc_prep_mel_launch(a->mel, B, cfg.in_channels, a->frames, a->pad, melc, d.planes, d.rows, halo, st);
+    }));
+  }
+  {
+    TcConvParams p = base(plan->tc_proj, sh.L0);
+    p.src[0] = src(melc, cfg.in_channels, sh.L0, cfg.proj_kernel, 1, -pp, false);
+    canon_out(p, cur, cfg.base_channels, sh.L0, true, 2);
+    const double macs = (double)cfg.proj_kernel * cfg.in_channels * cfg.base_channels * sh.L0 * B;
+    if (int rc = run("bf16.proj.k7", 1, p, macs,
+                     (double)B * (cfg.in_channels + cfg.base_channels) * sh.L0 +
+                         (double)cfg.proj_kernel * cfg.in_channels * cfg.base_channels))
+      return rc;
+    if (int rc = tap(1, cur, cfg.base_channels, sh.L0, true)) return rc;
+  }
+  int64_t Lin = sh.L0;
+  for (int s = 0; s < S; ++s) {
+    const StagePlan& sp = plan->stages[s];
+    const int64_t L = sh.L[s];
+    const int C = sp.Cout;
+    const bool last_stage = s == S - 1;
+    {
+      TcConvParams p = base(sp.tc_up, Lin);
+      p.src[0] = src(cur, sp.Cin, Lin, 2, -1, 0, false, 1);   // taps read x[m + q], x[m + q - 1], q in {0, 1}
+      // consumer: block 0 (raw x + reflect) or, with no blocks, the next transposed conv / head
+      if (nb > 0) canon_out(p, nxt, C, L, false, 1);
+      else canon_out(p, nxt, C, L, true, last_stage ? 1 : 2);
+      const double macs = 2.0 * sp.f * sp.Cin * C * Lin * B;
+      if (int rc = run("bf16.upsample.convT", sp.layer_up, p, macs,
+                       (double)B * (sp.Cin * Lin + C * L) + 2.0 * sp.f * sp.Cin * C))
+        return rc;
+      std::swap(cur, nxt);
+      if (int rc = tap(sp.layer_up, cur, C, L, nb == 0)) return rc;
+    }
+    const int half = (cfg.res_kernel - 1) / 2;
+    for (int bi = 0; bi < nb; ++bi) {
+      const BlockPlan& bp = sp.blocks[bi];
+      const int d = bp.dilation;
+      {
+        TcConvParams p = base(bp.tc_conv1, L);
+        p.src[0] = src(cur, C, L, cfg.res_kernel, d, -half * d, true);
+        canon_out(p, hbuf, C, L, true, 0);
+        if (int rc = run("bf16.resblock.conv1_dilated", sp.layer_stack, p, (double)cfg.res_kernel * C * C * L * B,
+                         2.0 * B * C * L + (double)cfg.res_kernel * C * C))
+          return rc;
+      }
+      {
+        TcConvParams p = base(bp.tc_conv2s, L);
+        p.nsrc = 2;
+        p.src[0] = src(hbuf, C, L, 1, 1, 0, false);
+        p.src[1] = src(cur, C, L, 1, 1, 0, false);
+        const bool last_block = bi == nb - 1;
+        if (!last_block) canon_out(p, nxt, C, L, false, 1);
+        else canon_out(p, nxt, C, L, true, last_stage ? 1 : 2);
+        if (int rc = run("bf16.resblock.conv2+shortcut", sp.layer_stack, p, 2.0 * C * C * L * B,
+                         3.0 * B * C * L + 2.0 * C * C))
+          return rc;
+        std::swap(cur, nxt);
+      }
+    }
+    if (nb > 0)
+      if (int rc = tap(sp.layer_stack, cur, C, L, true)) return rc;
+    Lin = L;
+  }
+  {
+    const int Cl = plan->stages.back().Cout;
+    const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
+    float* dst = to_out ? a->out : headf;
+    TcConvParams p = base(plan->tc_head, Lin);
+    p.src[0] = src(cur, Cl, Lin, cfg.proj_kernel, 1, -pp, false);
+    p.out_mode = 1; p.out_f = dst; p.out_L = (int)Lin;
+    const int ih = 4 + 3 * S;
+    if (int rc = run("bf16.head.k7+tanh", ih, p, (double)cfg.proj_kernel * Cl * cfg.out_channels * Lin * B,
+                     (double)B * (Cl + 2.0 * cfg.out_channels) * Lin))
+      return rc;
+    if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
+    if (!to_out) {
+      const int N = cfg.pqmf_bands;
+      TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B, 8.0 * N * Lin * B, [&] {
+        return pqmf_synthesis_launch(headf, Wf + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, st);
+      }));
+    }
+  }
+  return 0;
+}

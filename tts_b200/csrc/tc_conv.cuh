@@ -1,0 +1,72 @@
+// Host-visible description of one launch of the tcgen05 implicit-GEMM convolution (conv_bf16_tc.cu).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ttsb {
+
+constexpr int TC_MAX_TAPS = 8;
+constexpr int TC_TILE_M = 128;   // output rows (time positions) per CTA = UMMA M
+constexpr int TC_KB = 64;        // channels per weight pipeline stage
+constexpr int TC_STAGES = 3;
+
+// Activations are "canonical": [batch][C_pad/8 planes][plane_rows][8] bf16, plane row = halo + t.
+struct TcSrc {
+  const __nv_bfloat16* x;
+  int64_t batch_stride;   // elements
+  int planes;             // C_pad / 8
+  int plane_rows;         // rows per plane in global memory
+  int row_base;           // global plane row of smem row 0 when t0 == 0  (= halo + min tap shift)
+  int rows;               // rows staged in shared memory (TC_TILE_M + tap span)
+  int taps;
+  int tap_row[TC_MAX_TAPS];  // smem row of output row 0 for tap j (before the group's shift)
+  int lrelu;              // LeakyReLU applied in shared memory before the MMAs read it
+};
+
+// One CTA column-group: <= 256 accumulator columns of the flattened [phase][C_out_pad] axis.
+struct TcGroup {
+  const __nv_bfloat16* w;  // [src][tap][C_pad/8][ncols][8]
+  const float* bias;       // [ncols]
+  int ncols;               // multiple of 16
+  int tap_shift;           // added to every tap row (transposed conv: q = (r+P)/f)
+  int phase_first;         // upsample phase of column 0
+  int ch_first;            // channel (within the phase) of column 0
+};
+
+constexpr int TC_MAX_GROUPS = 16;
+
+struct TcConvParams {
+  TcSrc src[2];
+  int nsrc;
+  TcGroup grp[TC_MAX_GROUPS];
+  int ngroups;
+  int Lt;                 // GEMM rows (input positions for transposed conv, else output positions)
+  int up_f;               // output row = m * up_f + phase
+  int cout_pad;           // columns per phase
+  // output
+  int out_mode;           // 0: canonical bf16   1: fp32 NCL + tanh
+  __nv_bfloat16* out_c;   // canonical out
+  int64_t out_batch_stride;
+  int out_plane_rows;
+  int out_halo;
+  int out_L;              // valid output rows
+  int out_lrelu;          // store LeakyReLU(y) (the only consumer wants the activated tensor)
+  int margin;             // 0 none, 1 reflect (halo rows mirror the interior), 2 zero (rows -1 and L)
+  float* out_f;           // fp32 NCL out [B][cout_real][out_L]
+  int cout_real;
+  float slope;
+};
+
+size_t tc_conv_smem_bytes(const TcConvParams& p);
+cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream);
+
+// mel fp32 [B][C][T] -> canonical bf16 with replicate padding `pad` folded in and reflect margins
+cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out,
+                               int planes, int plane_rows, int halo, cudaStream_t stream);
+// canonical bf16 -> fp32 NCL (per-layer parity taps); undo_lrelu inverts a stored activation
+cudaError_t tc_untile_launch(const __nv_bfloat16* x, int batch, int C, int64_t L, int planes, int plane_rows,
+                             int halo, int undo_lrelu, float slope, float* out, cudaStream_t stream);
+
+}  // namespace ttsb

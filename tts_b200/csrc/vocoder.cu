@@ -272,6 +272,8 @@ int forward_f32(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   return 0;
 }
 
+#include "schedule_bf16.inl"
+
 }  // namespace
 }  // namespace ttsb
 
@@ -356,7 +358,13 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
     ti += 1;
   }
   plan->hop_generator = hop;
+  Bf16Builder b16;
+  if (int rc = pack_bf16(plan, tensors, bb, b16)) {
+    delete plan;
+    return rc;
+  }
   plan->blob_floats = bb.data.size();
+  plan->blob16_elems = b16.data.size();
 
   int prev = 0;
   cudaGetDevice(&prev);
@@ -364,9 +372,13 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
   if (e == cudaSuccess) e = cudaMalloc(&plan->blob, plan->blob_floats * sizeof(float));
   if (e == cudaSuccess)
     e = cudaMemcpy(plan->blob, bb.data.data(), plan->blob_floats * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc(&plan->blob16, plan->blob16_elems * sizeof(__nv_bfloat16));
+  if (e == cudaSuccess)
+    e = cudaMemcpy(plan->blob16, b16.data.data(), plan->blob16_elems * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice);
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
     if (plan->blob) cudaFree(plan->blob);
+    if (plan->blob16) cudaFree(plan->blob16);
     delete plan;
     return fail(TTSB200_ERR_CUDA, std::string("plan upload: ") + cudaGetErrorString(e));
   }
@@ -377,6 +389,7 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
 void ttsb200_plan_destroy(ttsb200_plan* plan) {
   if (!plan) return;
   if (plan->blob) cudaFree(plan->blob);
+  if (plan->blob16) cudaFree(plan->blob16);
   if (plan->host.d_in) cudaFree(plan->host.d_in);
   if (plan->host.d_out) cudaFree(plan->host.d_out);
   if (plan->host.d_ws) cudaFree(plan->host.d_ws);
@@ -399,7 +412,7 @@ int64_t ttsb200_workspace_bytes(const ttsb200_plan* plan, int32_t batch, int32_t
   if (!plan) return fail(TTSB200_ERR_INVALID, "plan is NULL");
   if (batch <= 0 || frames <= 0 || pad < 0) return fail(TTSB200_ERR_INVALID, "batch/frames must be positive, pad >= 0");
   const Shape sh = shapes_for(plan, frames, pad);
-  (void)precision;
+  if (precision == TTSB200_BF16) return (int64_t)bf16_workspace(plan, batch, sh).total_bytes;
   return 3 * round_up((int64_t)batch * sh.max_act, 64) * (int64_t)sizeof(float);
 }
 
@@ -440,7 +453,7 @@ int32_t ttsb200_generator_forward(const ttsb200_plan* plan, const ttsb200_forwar
     return fail(TTSB200_ERR_INVALID, "batch too large for one launch (batch * max upsample factor > 65535); split the batch");
   switch (a->precision) {
     case TTSB200_F32: return forward_f32(plan, a);
-    case TTSB200_BF16: return fail(TTSB200_ERR_INVALID, "BF16 tcgen05 path not built into this library yet");
+    case TTSB200_BF16: return forward_bf16(plan, a);
     default: return fail(TTSB200_ERR_INVALID, "unknown precision");
   }
 }
@@ -546,9 +559,9 @@ int32_t ttsb200_profile_read(ttsb200_profile* p, ttsb200_launch_record* records,
 
 int32_t ttsb200_launch_count(const ttsb200_plan* plan, int32_t precision, int32_t skip_pqmf) {
   if (!plan) return fail(TTSB200_ERR_INVALID, "plan is NULL");
-  (void)precision;
   const int S = plan->cfg.n_stages, n = plan->cfg.num_res_blocks;
-  return 1 + S * (1 + 2 * n) + 1 + ((plan->cfg.pqmf_bands > 0 && !skip_pqmf) ? 1 : 0);
+  return (precision == TTSB200_BF16 ? 1 : 0) + 1 + S * (1 + 2 * n) + 1 +
+         ((plan->cfg.pqmf_bands > 0 && !skip_pqmf) ? 1 : 0);
 }
 
 }  // extern "C"
