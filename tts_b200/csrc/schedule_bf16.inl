@@ -145,8 +145,38 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
                                [&](int co) { return b[co]; }))
       return rc;
   }
-  plan->halo = (int)round_up(std::max(max_d, 1), 8);
+  const int half = (cfg.res_kernel - 1) / 2;
+  int sum_d = 0;
+  for (int bi = 0; bi < cfg.num_res_blocks; ++bi) sum_d += half * (int)ipow(cfg.res_kernel, bi);
+  plan->halo = (int)round_up(std::max(std::max(max_d, sum_d), 1), 8);
   return 0;
+}
+
+// Fused-stack tiling for stage s, or kt == 0 when the stage must use the per-conv kernels.
+struct StackTiling {
+  int kt = 0, sum_d = 0, guard = 0, cp = 0;
+};
+StackTiling stack_tiling(const ttsb200_plan* plan, int s) {
+  const ttsb200_generator_config& cfg = plan->cfg;
+  StackTiling t;
+  const int nb = cfg.num_res_blocks, half = (cfg.res_kernel - 1) / 2;
+  t.cp = pad16(plan->stages[s].Cout);
+  if (nb < 1 || nb > TC_STACK_MAX_BLOCKS || t.cp > 96 || cfg.res_kernel > TC_MAX_TAPS) return t;
+  int dmax = 0;
+  for (int bi = 0; bi < nb; ++bi) {
+    t.sum_d += half * plan->stages[s].blocks[bi].dilation;
+    dmax = std::max(dmax, half * plan->stages[s].blocks[bi].dilation);
+  }
+  t.guard = (int)round_up(std::max(dmax, 1), 8);
+  for (int kt = t.sum_d <= 16 ? 2 : 4; kt >= 1; --kt) {
+    TcStackParams q{};
+    q.cp = t.cp; q.kt = kt; q.guard = t.guard; q.res_taps = cfg.res_kernel;
+    if (2 * kt * t.cp <= 512 && tc_stack_smem_bytes(q) <= 219 * 1024 && kt * 128 - 2 * t.sum_d >= 32) {
+      t.kt = kt;
+      break;
+    }
+  }
+  return t;
 }
 
 struct CanonDims {
@@ -156,7 +186,7 @@ struct CanonDims {
 inline CanonDims canon_dims(const ttsb200_plan* plan, int C, int64_t L) {
   CanonDims d;
   d.planes = pad16(C) / 8;
-  d.rows = (int)round_up(L, TC_TILE_M) + 2 * plan->halo;
+  d.rows = (int)round_up(L, TC_TILE_M) + 2 * plan->halo + 128 * TC_STACK_MAX_KT;  // slack: whole-tile bulk loads
   d.elems = (size_t)d.planes * d.rows * 8;
   return d;
 }
@@ -280,6 +310,28 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       if (int rc = tap(sp.layer_up, cur, C, L, nb == 0)) return rc;
     }
     const int half = (cfg.res_kernel - 1) / 2;
+    const StackTiling tl = stack_tiling(plan, s);
+    if (tl.kt > 0) {  // whole ResidualStack in one kernel, activations resident in shared memory
+      const CanonDims din = canon_dims(plan, C, L);
+      TcStackParams q{};
+      q.x = cur; q.x_batch_stride = (int64_t)din.elems; q.x_plane_rows = din.rows; q.x_halo = halo;
+      q.cp = tl.cp; q.L = (int)L; q.nblocks = nb; q.res_taps = cfg.res_kernel;
+      q.kt = tl.kt; q.sum_d = tl.sum_d; q.guard = tl.guard; q.slope = slope;
+      for (int bi = 0; bi < nb; ++bi) {
+        const BlockPlan& bp = sp.blocks[bi];
+        q.dil[bi] = bp.dilation;
+        q.w1[bi] = Wh + bp.tc_conv1.groups[0].w_off;
+        q.w2s[bi] = Wh + bp.tc_conv2s.groups[0].w_off;
+        q.b1[bi] = Wf + bp.tc_conv1.groups[0].bias_off;
+        q.b2s[bi] = Wf + bp.tc_conv2s.groups[0].bias_off;
+      }
+      q.out = TcCanonOut{nxt, (int64_t)din.elems, din.rows, halo, (int)L, 1, last_stage ? 1 : 2};
+      const double macs = (double)(cfg.res_kernel + 2) * nb * C * C * L * B;
+      TTSB_CUDA(ln.run("bf16.resstack.fused", sp.layer_stack, 2 * macs,
+                       2.0 * (2.0 * B * C * L + (double)(cfg.res_kernel + 2) * nb * C * C),
+                       [&] { return tc_stack_launch(q, B, st); }));
+      std::swap(cur, nxt);
+    } else
     for (int bi = 0; bi < nb; ++bi) {
       const BlockPlan& bp = sp.blocks[bi];
       const int d = bp.dilation;

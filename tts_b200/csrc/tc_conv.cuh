@@ -59,6 +59,44 @@ struct TcConvParams {
   float slope;
 };
 
+// Where a kernel's result goes: canonical bf16 for the next tcgen05 kernel (halo rows filled per the
+// consumer's padding rule), shared by the conv and the fused-stack kernels.
+struct TcCanonOut {
+  __nv_bfloat16* base;     // batch 0
+  int64_t batch_stride;    // elements
+  int plane_rows;
+  int halo;
+  int L;                   // valid rows
+  int lrelu;               // store LeakyReLU(y)
+  int margin;              // 0 none, 1 reflect, 2 zero rows at -1 and L
+};
+
+// Fused ResidualStack (melgan.py:36-39): x <- S_b x + W2_b lrelu(W1_b * lrelu(x)) for b = 0..n-1 in ONE
+// kernel, activations resident in shared memory, accumulators in TMEM.
+constexpr int TC_STACK_MAX_BLOCKS = 4;
+constexpr int TC_STACK_MAX_KT = 4;
+struct TcStackParams {
+  const __nv_bfloat16* x;  // canonical raw input (no margins needed)
+  int64_t x_batch_stride;
+  int x_plane_rows, x_halo;
+  int cp;                  // padded channels (multiple of 16, <= 96)
+  int L;                   // sequence length
+  int nblocks;
+  int res_taps;            // res_kernel (odd)
+  int dil[TC_STACK_MAX_BLOCKS];
+  const __nv_bfloat16* w1[TC_STACK_MAX_BLOCKS];   // [tap][cp/8][cp][8]
+  const __nv_bfloat16* w2s[TC_STACK_MAX_BLOCKS];  // [2][cp/8][cp][8]  (conv 1x1, shortcut 1x1)
+  const float* b1[TC_STACK_MAX_BLOCKS];           // [cp]
+  const float* b2s[TC_STACK_MAX_BLOCKS];          // [cp]  conv2.bias + shortcut.bias
+  int kt;                  // 128-row M tiles per CTA
+  int sum_d;               // one-sided receptive field of the stack = sum over blocks of half*dil
+  int guard;               // spare rows either side of the staged tile (>= max dilation reach)
+  TcCanonOut out;
+  float slope;
+};
+size_t tc_stack_smem_bytes(const TcStackParams& p);
+cudaError_t tc_stack_launch(const TcStackParams& p, int batch, cudaStream_t stream);
+
 size_t tc_conv_smem_bytes(const TcConvParams& p);
 cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream);
 

@@ -560,8 +560,10 @@ int32_t ttsb200_profile_read(ttsb200_profile* p, ttsb200_launch_record* records,
 int32_t ttsb200_launch_count(const ttsb200_plan* plan, int32_t precision, int32_t skip_pqmf) {
   if (!plan) return fail(TTSB200_ERR_INVALID, "plan is NULL");
   const int S = plan->cfg.n_stages, n = plan->cfg.num_res_blocks;
-  return (precision == TTSB200_BF16 ? 1 : 0) + 1 + S * (1 + 2 * n) + 1 +
-         ((plan->cfg.pqmf_bands > 0 && !skip_pqmf) ? 1 : 0);
+  int launches = 1 + S + 1 + ((plan->cfg.pqmf_bands > 0 && !skip_pqmf) ? 1 : 0);
+  for (int s = 0; s < S; ++s)
+    launches += (precision == TTSB200_BF16 && n > 0 && stack_tiling(plan, s).kt > 0) ? 1 : 2 * n;
+  return launches + (precision == TTSB200_BF16 ? 1 : 0);
 }
 
 }  // extern "C"
