@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
   const uint32_t tbase = tmem_base_s;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       // ---- activation tile(s): one bulk copy per 8-channel plane
       mbar_expect_tx(&bar_a, a_bytes0 + a_bytes1);
       for (int s = 0; s < p.nsrc; ++s) {
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       if (need_lrelu) mbar_wait(&bar_a_ready, 0); else mbar_wait(&bar_a, 0);
       tc_fence_after();
       const uint32_t idesc = make_idesc_bf16(TC_TILE_M, ncols);

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(NT) tc_stack_kernel(const __grid_constant__ Tc
   const uint32_t tbase = tmem_base_s;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       // stage input tile: rows g0 .. g0+TR of every plane, into XR at staged row G
       mbar_expect_tx(&bars.x, (uint32_t)planes * TR * 16);
       const __nv_bfloat16* gx = p.x + (int64_t)b * p.x_batch_stride + (int64_t)(p.x_halo + g0) * 8;
@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(NT) tc_stack_kernel(const __grid_constant__ Tc
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(128, cp);
       const uint32_t lbo_a = plane_bytes, lbo_b = (uint32_t)cp * 16;
       const uint32_t xa = smem_u32(sXA), xr = smem_u32(sXR), w1 = smem_u32(sW1), w2 = smem_u32(sW2);
