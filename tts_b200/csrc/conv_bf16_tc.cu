@@ -25,14 +25,6 @@ namespace {
 
 constexpr int NT = 192;
 
-__device__ __forceinline__ float lrelu_f(float v, float s) { return v >= 0.f ? v : v * s; }
-
-__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t u, float slope) {
-  const float lo = lrelu_f(__uint_as_float(u << 16), slope);
-  const float hi = lrelu_f(__uint_as_float(u & 0xFFFF0000u), slope);
-  return pack_bf16x2(lo, hi);
-}
-
 __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcConvParams p, const int w_stage_bytes,
                                                       const int nst) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -139,6 +131,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
     // ---- warps 2..5: optional LeakyReLU over the staged tile, then the epilogue
     const int et = tid - 64;
     if (need_lrelu) {
+      const Slope2 slope2 = make_slope2(p.slope);
       mbar_wait(&bar_a, 0);
       for (int s = 0; s < p.nsrc; ++s) {
         if (!p.src[s].lrelu) continue;
@@ -146,8 +139,8 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
         const int nvec = (s ? a_bytes1 : a_bytes0) / 16;
         for (int e = et; e < nvec; e += 128) {
           uint4 u = v[e];
-          u.x = lrelu_bf16x2(u.x, p.slope); u.y = lrelu_bf16x2(u.y, p.slope);
-          u.z = lrelu_bf16x2(u.z, p.slope); u.w = lrelu_bf16x2(u.w, p.slope);
+          u.x = lrelu_bf16x2(u.x, slope2); u.y = lrelu_bf16x2(u.y, slope2);
+          u.z = lrelu_bf16x2(u.z, slope2); u.w = lrelu_bf16x2(u.w, slope2);
           v[e] = u;
         }
       }

@@ -23,7 +23,8 @@ constexpr int TN = 128;  // time positions per CTA
 constexpr int BK = 16;   // input channels per K slice
 constexpr int NT = 256;  // threads per CTA
 
-__device__ __forceinline__ float lrelu_f(float v, float slope) { return v >= 0.f ? v : v * slope; }
+// 0 <= slope <= 1 (validated at plan creation), so lrelu(v) = max(v, slope v): no predicate chain
+__device__ __forceinline__ float lrelu_f(float v, float slope) { return fmaxf(v, v * slope); }
 
 // Resolve a virtual position to a stored column; returns -1 for "contributes zero".
 __device__ __forceinline__ int resolve_pos(const ConvSrc& s, int pos) {

@@ -152,31 +152,17 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
   return 0;
 }
 
-// Fused-stack tiling for stage s, or kt == 0 when the stage must use the per-conv kernels.
-struct StackTiling {
-  int kt = 0, sum_d = 0, guard = 0, cp = 0;
-};
-StackTiling stack_tiling(const ttsb200_plan* plan, int s) {
+// Fused-stack configuration for stage s; kt == 0 when the stage must use the per-conv kernels.
+TcStackParams stack_tiling(const ttsb200_plan* plan, int s) {
   const ttsb200_generator_config& cfg = plan->cfg;
-  StackTiling t;
-  const int nb = cfg.num_res_blocks, half = (cfg.res_kernel - 1) / 2;
-  t.cp = pad16(plan->stages[s].Cout);
-  if (nb < 1 || nb > TC_STACK_MAX_BLOCKS || t.cp > 96 || cfg.res_kernel > TC_MAX_TAPS) return t;
-  int dmax = 0;
-  for (int bi = 0; bi < nb; ++bi) {
-    t.sum_d += half * plan->stages[s].blocks[bi].dilation;
-    dmax = std::max(dmax, half * plan->stages[s].blocks[bi].dilation);
-  }
-  t.guard = (int)round_up(std::max(dmax, 1), 8);
-  for (int kt = t.sum_d <= 16 ? 2 : 4; kt >= 1; --kt) {
-    TcStackParams q{};
-    q.cp = t.cp; q.kt = kt; q.guard = t.guard; q.res_taps = cfg.res_kernel;
-    if (2 * kt * t.cp <= 512 && tc_stack_smem_bytes(q) <= 219 * 1024 && kt * 128 - 2 * t.sum_d >= 32) {
-      t.kt = kt;
-      break;
-    }
-  }
-  return t;
+  TcStackParams q{};
+  q.cp = pad16(plan->stages[s].Cout);
+  q.nblocks = cfg.num_res_blocks;
+  q.res_taps = cfg.res_kernel;
+  if (q.nblocks < 1 || q.nblocks > TC_STACK_MAX_BLOCKS) return q;
+  for (int bi = 0; bi < q.nblocks; ++bi) q.dil[bi] = plan->stages[s].blocks[bi].dilation;
+  if (!tc_stack_configure(q)) q.kt = 0;
+  return q;
 }
 
 struct CanonDims {
@@ -310,16 +296,13 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       if (int rc = tap(sp.layer_up, cur, C, L, nb == 0)) return rc;
     }
     const int half = (cfg.res_kernel - 1) / 2;
-    const StackTiling tl = stack_tiling(plan, s);
-    if (tl.kt > 0) {  // whole ResidualStack in one kernel, activations resident in shared memory
+    TcStackParams q = stack_tiling(plan, s);
+    if (q.kt > 0) {  // whole ResidualStack in one kernel
       const CanonDims din = canon_dims(plan, C, L);
-      TcStackParams q{};
       q.x = cur; q.x_batch_stride = (int64_t)din.elems; q.x_plane_rows = din.rows; q.x_halo = halo;
-      q.cp = tl.cp; q.L = (int)L; q.nblocks = nb; q.res_taps = cfg.res_kernel;
-      q.kt = tl.kt; q.sum_d = tl.sum_d; q.guard = tl.guard; q.slope = slope;
+      q.L = (int)L; q.slope = slope;
       for (int bi = 0; bi < nb; ++bi) {
         const BlockPlan& bp = sp.blocks[bi];
-        q.dil[bi] = bp.dilation;
         q.w1[bi] = Wh + bp.tc_conv1.groups[0].w_off;
         q.w2s[bi] = Wh + bp.tc_conv2s.groups[0].w_off;
         q.b1[bi] = Wf + bp.tc_conv1.groups[0].bias_off;

@@ -1,28 +1,39 @@
 // Fused ResidualStack on tcgen05 / TMEM (TTS/vocoder/layers/melgan.py:13-38): all n blocks
 //     x <- S_b x + W2_b lrelu( W1_b (*) lrelu(x)[reflect, dilation 3^b] + b1_b ) + (b2_b + bs_b)
-// of one upsampling stage run in ONE kernel on a time tile of kt*128 rows.  The stage input is read
-// from HBM once, every intermediate (x, lrelu(x), h) lives in shared memory in the canonical UMMA
-// layout, accumulators live in TMEM, and only the stack output goes back to HBM.  Per tile the
-// valid region shrinks by the dilation reach of each block (halo recompute, sum_d rows per side).
+// of one upsampling stage run in ONE persistent kernel.  A work item is a chain of KT adjacent 128-row time
+// tiles of one utterance; the stage input is read from HBM once, only the stack output goes back.
 //
-// Shared-memory tensors ([cp/8 planes][RS rows][8 ch] bf16, RS = kt*128 + 2*guard):
-//   XR  raw x           — A operand of the 1x1 shortcut, overwritten in place by each block's output
-//   XA  lrelu(x)        — A operand of the dilated conv (taps = start-row offsets); after that
-//                          conv has been issued for the whole tile the same buffer holds h = lrelu(.)
-//                          (A operand of the 1x1 conv) and is then refilled with lrelu(x_new)
-//   W1 / W2S            — weights of the current block; the next block's are fetched by the bulk-copy
-//                          engine as soon as the MMAs that read the buffer have retired
-// TMEM: D1[t] (dilated conv) and D2[t] (1x1 + shortcut) for each of the kt row tiles.
+// Where every tensor lives while an item is in flight:
+//   XA   (shared, canonical [CP/8][RS][8] bf16, double-buffered across items)  lrelu(x): A operand of the
+//        dilated conv — each tap is the same tile at a different start row, so only the descriptor moves;
+//   XR[t] (TMEM, bf16, CP/2 columns)  raw x of tile t: A operand of the 1x1 shortcut (A-from-TMEM MMA);
+//   D1[t] (TMEM, fp32, CP columns)    dilated-conv accumulator; its epilogue writes h = lrelu(D1 + b1) as bf16
+//        over the low CP/2 columns of the same region -> A operand of the 1x1 conv, never touching smem;
+//   D2[t] (TMEM, fp32, CP columns)    W2 h + S x accumulator = x of the next block.
+//   W1 / W2S (shared)  weights of the current block, or of all blocks when they fit (then loaded once per CTA).
+// Only lrelu(x_new) makes the round trip registers -> shared memory; h and x never leave the tensor-core side.
 //
-// Sequence edges: ReflectionPad1d precedes every dilated conv, so before each block the rows just
-// outside [0, L) are rewritten with the mirror of the rows just inside (only in CTAs that see an edge).
+// Pipeline: the MMA thread issues, per block, the dilated conv of tiles 0..KT-1 and then the 1x1 pair of tiles
+// 0..KT-1; tcgen05 executes in issue order, so epilogue 1 of tile t overlaps the dilated conv of tile t+1 and
+// epilogue 2 of tile t overlaps the 1x1 MMAs of tile t+1.  Tile t of the next block starts as soon as tiles
+// t-1, t, t+1 have been rewritten (per-tile mbarriers), not when the whole block is done.
 //
-// Warps: 0 = bulk-copy producer + TMEM owner, 1 = MMA issuer, 2..9 = prologue/epilogue (two warps per
-// TMEM lane quarter, splitting the 16-column chunks).
+// Sequence edges: ReflectionPad1d precedes every dilated conv.  Threads whose row lies within `guard` rows of
+// an edge also write it to its mirror position; rows outside [0, L) are never written by their owners.  Tile
+// (not sequence) boundaries get true neighbours: a chain recomputes sum_d halo rows per side.
+//
+// Warps: KT epilogue groups of 4*CS warps, then the bulk-copy producer (+ TMEM owner) and the MMA issuer as the
+// two highest warp ids (the SMSP arbiter favours high ids, so the issuer is never starved).  Group t
+// owns tile t (prologue, both epilogues of every block), one warp per TMEM lane quarter and channel split.
+// Tiles therefore advance as independent chains: the latency of one tile's epilogue (barrier -> tcgen05.ld ->
+// math -> tcgen05.st -> barrier) hides behind the MMAs and epilogues of the other tiles.
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "tc_conv.cuh"
-#include "tc_store.cuh"
 
 namespace ttsb {
 
@@ -30,256 +41,470 @@ using namespace tc;
 
 namespace {
 
-constexpr int NT = 320;
-constexpr int EPI_THREADS = 256;
+constexpr int TAPS = 3;
+constexpr int MAX_KT = TC_STACK_MAX_KT;
 
-__device__ __forceinline__ float lrelu_f(float v, float s) { return v >= 0.f ? v : v * s; }
-__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t u, float slope) {
-  return pack_bf16x2(lrelu_f(__uint_as_float(u << 16), slope), lrelu_f(__uint_as_float(u & 0xFFFF0000u), slope));
+
+// Timeline capture for CTA 0 (debug aid, enabled by TTSB200_STACK_TRACE=<file>): role r appends {tag, clock64}.
+#ifdef TTSB_STACK_TRACE
+struct Tracer {
+  long long* buf;
+  int n;
+  __device__ __forceinline__ void operator()(int tag) {
+    if (buf && n < 254) {
+      buf[n] = tag;
+      buf[n + 1] = clock64();
+      n += 2;
+    }
+  }
+};
+__device__ __forceinline__ Tracer make_tracer(const TcStackParams& p, int role, bool leader) {
+  return Tracer{(p.trace && blockIdx.x == 0 && leader) ? p.trace + role * 256 : nullptr, 0};
 }
-__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+#else   // compiled out: the trace points cost instruction-cache space in a kernel that is sensitive to it
+struct Tracer {
+  __device__ __forceinline__ void operator()(int) {}
+};
+__device__ __forceinline__ Tracer make_tracer(const TcStackParams&, int, bool) { return Tracer{}; }
+#endif
 
 struct Bars {
-  uint64_t x, xready, w1, w2, w1_free, w2_free;
-  uint64_t d1[TC_STACK_MAX_KT], h[TC_STACK_MAX_KT], d2[TC_STACK_MAX_KT];
+  uint64_t x_full[2], x_free[2];
+  uint64_t w1_full[TC_STACK_MAX_BLOCKS], w2_full[TC_STACK_MAX_BLOCKS], w1_free, w2_free;
+  uint64_t xa_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
 };
 
-__global__ void __launch_bounds__(NT) tc_stack_kernel(const __grid_constant__ TcStackParams p) {
+template <int CP, int KT, int CS>
+__global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const __grid_constant__ TcStackParams p) {
+  constexpr int NT = 64 + KT * CS * 128;
+  constexpr int GROUP_THREADS = CS * 128;
+  constexpr int PL = CP / 8;          // 8-channel planes
+  constexpr int KS = CP / 16;         // K = 16 steps per tap
+  constexpr int TR = KT * 128;        // staged rows owned by the chain
+  constexpr int CW = CP / CS;         // channels per epilogue thread
+  constexpr int TCOLS = 5 * CP / 2;   // TMEM columns per tile: D1 | D2 | XR
+  static_assert(KT * TCOLS <= 512, "TMEM budget");
+  static_assert(CW % 8 == 0, "CP must be a multiple of 16");
+
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) Bars bars;
   __shared__ uint32_t tmem_base_s;
-  __shared__ float s_bias[TC_STACK_MAX_BLOCKS][2][96];
+  __shared__ __align__(16) float s_bias[TC_STACK_MAX_BLOCKS][2][CP];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int cp = p.cp, kt = p.kt, planes = cp >> 3;
-  const int TR = kt * 128, RS = TR + 2 * p.guard, G = p.guard;
-  const int V = TR - 2 * p.sum_d;                  // rows of final output this CTA owns
-  const int g0 = blockIdx.x * V - p.sum_d;         // sequence row of staged row 0
-  const int b = blockIdx.y;
-  const int half = (p.res_taps - 1) / 2;
-
+  const int G = p.guard, RS = TR + 2 * G;
+  const int V = TR - 2 * p.sum_d;
+  const int nb = p.nblocks;
   const uint32_t plane_bytes = (uint32_t)RS * 16;
-  const uint32_t act_bytes = (uint32_t)planes * plane_bytes;
-  uint8_t* sXR = smem;
-  uint8_t* sXA = smem + act_bytes;
-  uint8_t* sW1 = smem + 2 * act_bytes;
-  const uint32_t w1_bytes = (uint32_t)p.res_taps * cp * cp * 2;
-  const uint32_t w2_bytes = 2u * cp * cp * 2;
-  uint8_t* sW2 = sW1 + w1_bytes;
+  const uint32_t xa_bytes = (uint32_t)PL * plane_bytes;
+  constexpr uint32_t W1_BYTES = TAPS * CP * CP * 2, W2_BYTES = 2 * CP * CP * 2;
+  const int wsets = p.w_sets;  // nb: every block's weights stay resident; 1: reloaded per block
+  uint8_t* sXA = smem;
+  uint8_t* sW = smem + 2 * xa_bytes;   // [set][W1 | W2S]
 
-  uint32_t tcols = 32;
-  while (tcols < (uint32_t)(2 * kt * cp)) tcols <<= 1;
+  const int n_items = p.n_chains * p.batch;
 
   if (tid == 0) {
-    mbar_init(&bars.x, 1);
-    mbar_init(&bars.xready, EPI_THREADS);
-    mbar_init(&bars.w1, 1);
-    mbar_init(&bars.w2, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars.x_full[i], 1);
+      mbar_init(&bars.x_free[i], 1);
+    }
+    for (int i = 0; i < TC_STACK_MAX_BLOCKS; ++i) {
+      mbar_init(&bars.w1_full[i], 1);
+      mbar_init(&bars.w2_full[i], 1);
+    }
     mbar_init(&bars.w1_free, 1);
     mbar_init(&bars.w2_free, 1);
-    for (int t = 0; t < kt; ++t) {
-      mbar_init(&bars.d1[t], 1);
-      mbar_init(&bars.h[t], EPI_THREADS);
-      mbar_init(&bars.d2[t], 1);
+    for (int t = 0; t < KT; ++t) {
+      mbar_init(&bars.xa_ready[t], GROUP_THREADS);
+      mbar_init(&bars.d1_full[t], 1);
+      mbar_init(&bars.h_ready[t], GROUP_THREADS);
+      mbar_init(&bars.d2_full[t], 1);
     }
     fence_mbar_init();
   }
-  if (warp == 0) tmem_alloc(&tmem_base_s, tcols);
+  constexpr int PRODUCER_WARP = KT * CS * 4, MMA_WARP = PRODUCER_WARP + 1;
+  if (warp == PRODUCER_WARP) tmem_alloc(&tmem_base_s, 512);
+  for (int e = tid; e < nb * 2 * CP; e += NT) {
+    const int blk = e / (2 * CP), r = e - blk * 2 * CP;
+    s_bias[blk][r / CP][r % CP] = r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP];
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
 
-  if (warp == 0) {
+  if (warp == PRODUCER_WARP) {
+    // =============================== producer ===============================
     if (elect_one()) {
-      // stage input tile: rows g0 .. g0+TR of every plane, into XR at staged row G
-      mbar_expect_tx(&bars.x, (uint32_t)planes * TR * 16);
-      const __nv_bfloat16* gx = p.x + (int64_t)b * p.x_batch_stride + (int64_t)(p.x_halo + g0) * 8;
-      for (int pl = 0; pl < planes; ++pl)
-        bulk_g2s(sXR + (size_t)pl * plane_bytes + (size_t)G * 16, gx + (int64_t)pl * p.x_plane_rows * 8,
-                 (uint32_t)TR * 16, &bars.x);
-      for (int blk = 0; blk < p.nblocks; ++blk) {
-        if (blk > 0) mbar_wait(&bars.w1_free, (blk - 1) & 1);
-        mbar_expect_tx(&bars.w1, w1_bytes);
-        bulk_g2s(sW1, p.w1[blk], w1_bytes, &bars.w1);
-        if (blk > 0) mbar_wait(&bars.w2_free, (blk - 1) & 1);
-        mbar_expect_tx(&bars.w2, w2_bytes);
-        bulk_g2s(sW2, p.w2s[blk], w2_bytes, &bars.w2);
+      auto load_x = [&](int it) {
+        const int item = blockIdx.x + it * gridDim.x;
+        if (item >= n_items) return;
+        const int buf = it & 1;
+        if (it >= 2) mbar_wait(&bars.x_free[buf], ((it >> 1) - 1) & 1);
+        const int b = item / p.n_chains, chain = item - b * p.n_chains;
+        const int g0 = chain * V - p.sum_d;
+        mbar_expect_tx(&bars.x_full[buf], (uint32_t)PL * TR * 16);
+        const __nv_bfloat16* gx = p.x + (int64_t)b * p.x_batch_stride + (int64_t)(p.x_halo + g0) * 8;
+        uint8_t* dst = sXA + (size_t)buf * xa_bytes + (size_t)G * 16;
+        for (int pl = 0; pl < PL; ++pl)
+          bulk_g2s(dst + (size_t)pl * plane_bytes, gx + (int64_t)pl * p.x_plane_rows * 8, (uint32_t)TR * 16,
+                   &bars.x_full[buf]);
+      };
+      load_x(0);
+      int gb = 0;
+      for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
+        for (int blk = 0; blk < nb; ++blk, ++gb) {
+          if (wsets == 1 || it == 0) {
+            const int set = wsets == 1 ? 0 : blk;
+            uint8_t* w1 = sW + (size_t)set * (W1_BYTES + W2_BYTES);
+            if (wsets == 1 && gb > 0) mbar_wait(&bars.w1_free, (gb - 1) & 1);
+            mbar_expect_tx(&bars.w1_full[set], W1_BYTES);
+            bulk_g2s(w1, p.w1[blk], W1_BYTES, &bars.w1_full[set]);
+            if (wsets == 1 && gb > 0) mbar_wait(&bars.w2_free, (gb - 1) & 1);
+            mbar_expect_tx(&bars.w2_full[set], W2_BYTES);
+            bulk_g2s(w1 + W1_BYTES, p.w2s[blk], W2_BYTES, &bars.w2_full[set]);
+          }
+          if (blk == 0) load_x(it + 1);   // prefetch the next item's tile behind this item's first weights
+        }
       }
     }
-  } else if (warp == 1) {
-    if (elect_one()) {
-      const uint32_t idesc = make_idesc_bf16(128, cp);
-      const uint32_t lbo_a = plane_bytes, lbo_b = (uint32_t)cp * 16;
-      const uint32_t xa = smem_u32(sXA), xr = smem_u32(sXR), w1 = smem_u32(sW1), w2 = smem_u32(sW2);
-      const int ksteps = cp >> 4;
-      for (int blk = 0; blk < p.nblocks; ++blk) {
-        const uint32_t ph = blk & 1;
-        const int d = p.dil[blk];
-        mbar_wait(&bars.xready, ph);
-        mbar_wait(&bars.w1, ph);
-        tc_fence_after();
-        for (int t = 0; t < kt; ++t) {                 // dilated conv: taps are start-row offsets into XA
-          uint32_t acc = 0;
-          for (int j = 0; j < p.res_taps; ++j) {
-            const uint32_t a_row = xa + (uint32_t)(G + t * 128 + (j - half) * d) * 16;
-            const uint32_t w_tap = w1 + (uint32_t)j * cp * cp * 2;
-            for (int kk = 0; kk < ksteps; ++kk) {
-              umma_bf16(tbase + t * cp, make_desc(a_row + 2 * kk * lbo_a, lbo_a, 128),
-                        make_desc(w_tap + 2 * kk * lbo_b, lbo_b, 128), idesc, acc);
-              acc = 1;
+  } else if (warp == MMA_WARP) {
+    // =============================== MMA issuer ===============================
+    // The whole warp walks the loops (uniform control flow keeps addresses in uniform registers, so an MMA
+    // costs a couple of uniform adds); only the tcgen05 instructions themselves are issued by the elected lane.
+    {
+      const bool leader = elect_one() != 0;
+      constexpr uint32_t idesc = make_idesc_bf16(128, CP);
+      constexpr uint32_t LBO_B = CP * 16;
+      const uint32_t lbo_a = plane_bytes;
+      // descriptor templates: only the 14-bit start-address field changes between MMAs
+      const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
+      Tracer tr = make_tracer(p, 0, leader);
+      int gb = 0;
+      for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
+        const int buf = it & 1;
+        const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
+        for (int blk = 0; blk < nb; ++blk, ++gb) {
+          const uint32_t ph = gb & 1;
+          const int set = wsets == 1 ? 0 : blk;
+          const uint32_t w1 = smem_u32(sW + (size_t)set * (W1_BYTES + W2_BYTES)), w2 = w1 + W1_BYTES;
+          const int d = p.dil[blk];
+          // ---- dilated conv: D1[t] = sum_tap XA[rows + (tap-1) d] W1[tap]^T
+          if (wsets == 1) mbar_wait(&bars.w1_full[0], ph);
+          else if (it == 0) mbar_wait(&bars.w1_full[set], 0);
+#pragma unroll 1
+          for (int t = 0; t < KT; ++t) {
+            if (t == 0) mbar_wait(&bars.xa_ready[0], ph);
+            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], ph);
+            tc_fence_after();
+            tr(100 + t);
+            const uint32_t dcol = tbase + t * TCOLS;
+            if (leader) {
+#pragma unroll
+              for (int j = 0; j < TAPS; ++j) {
+                const uint32_t a_row = xa + (uint32_t)(G + t * 128 + (j - 1) * d) * 16;
+                const uint32_t w_tap = w1 + (uint32_t)j * (CP * CP * 2);
+#pragma unroll
+                for (int kk = 0; kk < KS; ++kk)
+                  umma_bf16(dcol, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
+                            b_tmpl | (uint64_t)((w_tap + 2 * kk * LBO_B) >> 4), idesc, (j | kk) != 0);
+              }
+              umma_commit(&bars.d1_full[t]);
             }
+            __syncwarp();
+            tr(110 + t);
           }
-          umma_commit(&bars.d1[t]);
-        }
-        umma_commit(&bars.w1_free);
-        mbar_wait(&bars.w2, ph);
-        for (int t = 0; t < kt; ++t) {                 // 1x1 on h (in the XA buffer) + 1x1 shortcut on raw x
-          mbar_wait(&bars.h[t], ph);
-          tc_fence_after();
-          const uint32_t row = (uint32_t)(G + t * 128) * 16;
-          uint32_t acc = 0;
-          for (int s = 0; s < 2; ++s) {
-            const uint32_t a_row = (s ? xr : xa) + row;
-            const uint32_t w_s = w2 + (uint32_t)s * cp * cp * 2;
-            for (int kk = 0; kk < ksteps; ++kk) {
-              umma_bf16(tbase + (kt + t) * cp, make_desc(a_row + 2 * kk * lbo_a, lbo_a, 128),
-                        make_desc(w_s + 2 * kk * lbo_b, lbo_b, 128), idesc, acc);
-              acc = 1;
+          if (leader) {
+            if (wsets == 1) umma_commit(&bars.w1_free);
+            if (blk == nb - 1) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
+          }
+          __syncwarp();
+          // ---- 1x1 conv on h (TMEM) + 1x1 shortcut on raw x (TMEM): D2[t]
+          if (wsets == 1) mbar_wait(&bars.w2_full[0], ph);
+          else if (it == 0) mbar_wait(&bars.w2_full[set], 0);
+#pragma unroll 1
+          for (int t = 0; t < KT; ++t) {
+            mbar_wait(&bars.h_ready[t], ph);
+            tc_fence_after();
+            tr(120 + t);
+            const uint32_t tcol = tbase + t * TCOLS;
+            if (leader) {
+#pragma unroll
+              for (int kk = 0; kk < KS; ++kk)
+                umma_bf16_ts(tcol + CP, tcol + 8 * kk, b_tmpl | (uint64_t)((w2 + 2 * kk * LBO_B) >> 4), idesc, kk != 0);
+#pragma unroll
+              for (int kk = 0; kk < KS; ++kk)
+                umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
+                             b_tmpl | (uint64_t)((w2 + CP * CP * 2 + 2 * kk * LBO_B) >> 4), idesc, 1);
+              umma_commit(&bars.d2_full[t]);
             }
+            __syncwarp();
+            tr(130 + t);
           }
-          umma_commit(&bars.d2[t]);
+          if (leader && wsets == 1) umma_commit(&bars.w2_free);
+          __syncwarp();
         }
-        umma_commit(&bars.w2_free);
       }
     }
   } else {
-    // ---------------- warps 2..9: prologue + epilogues ----------------
-    const int et = tid - 64;                    // 0..255
-    const int q4 = warp & 3;                    // TMEM lane quarter
-    const int hf = (warp - 2) >> 2;             // which half of the 16-column chunks
-    const int m = q4 * 32 + lane;               // row within a 128-row tile
-    const uint32_t tlane = tbase + ((uint32_t)(q4 * 32) << 16);
-    const int nchunks = cp >> 4;
+    // =============================== epilogue warps ===============================
+    const int q4 = warp & 3;                    // TMEM lane quarter this warp may touch
+    const int t = warp / (4 * CS);              // the tile this warp's group owns
+    const int cs = (warp / 4) % CS;             // which slice of the channels
+    const int m = q4 * 32 + lane;               // row within the 128-row tile
+    const uint32_t tlane = tbase + ((uint32_t)(q4 * 32) << 16) + t * TCOLS;
+    const int c0 = cs * CW;                     // first channel of this thread
+    const float slope = p.slope;
+    const Slope2 slope2 = make_slope2(slope);
+    const int L = p.L;
+    const int pair_bar = 1 + t * 4 + q4;        // named barrier shared by the CS warps of a quarter
+    Tracer tr = make_tracer(p, 1 + t, m == 0 && cs == 0);
 
-    for (int e = et; e < p.nblocks * 2 * cp; e += EPI_THREADS) {
-      const int blk = e / (2 * cp), r = e - blk * 2 * cp;
-      s_bias[blk][r / cp][r % cp] = r < cp ? p.b1[blk][r] : p.b2s[blk][r - cp];
-    }
+    int gb = 0;
+    for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
+      const int item = blockIdx.x + it * gridDim.x;
+      const int buf = it & 1;
+      const int b = item / p.n_chains, chain = item - b * p.n_chains;
+      const int g0 = chain * V - p.sum_d;       // sequence row of staged row 0
+      uint8_t* xa = sXA + (size_t)buf * xa_bytes + (size_t)(c0 / 8) * plane_bytes;   // this thread's first plane
 
-    // rows just outside the sequence <- mirror of the rows just inside (ReflectionPad1d), for dilation d
-    auto mirror = [&](int d) {
-      const bool left = g0 < 0, right = g0 + TR > p.L;
-      if (!left && !right) return;
-      const int per_side = half * d * planes * 2;
-      for (int e = et; e < 2 * per_side; e += EPI_THREADS) {
-        const int side = e / per_side, r = e - side * per_side;
-        if (side == 0 ? !left : !right) continue;
-        const int buf = r & 1, q = r >> 1, pl = q % planes, i = q / planes + 1;
-        const int dst = (side == 0 ? -i : p.L - 1 + i) - g0, src = (side == 0 ? i : p.L - 1 - i) - g0;
-        if (dst < -G || dst >= TR + G || src < 0 || src >= TR) continue;
-        uint8_t* base = (buf ? sXA : sXR) + (size_t)pl * plane_bytes;
-        *reinterpret_cast<uint4*>(base + (size_t)(G + dst) * 16) = *reinterpret_cast<const uint4*>(base + (size_t)(G + src) * 16);
-      }
-    };
-
-    // prologue: XA = lrelu(XR) over the staged rows
-    mbar_wait(&bars.x, 0);
-    for (int e = et; e < planes * TR; e += EPI_THREADS) {
-      const int pl = e / TR, r = e - pl * TR;
-      const size_t off = (size_t)pl * plane_bytes + (size_t)(G + r) * 16;
-      uint4 u = *reinterpret_cast<const uint4*>(sXR + off);
-      u.x = lrelu_bf16x2(u.x, p.slope); u.y = lrelu_bf16x2(u.y, p.slope);
-      u.z = lrelu_bf16x2(u.z, p.slope); u.w = lrelu_bf16x2(u.w, p.slope);
-      *reinterpret_cast<uint4*>(sXA + off) = u;
-    }
-    epi_barrier();
-    mirror(p.dil[0]);
-    fence_proxy_async();
-    mbar_arrive(&bars.xready);
-
-    for (int blk = 0; blk < p.nblocks; ++blk) {
-      const uint32_t ph = blk & 1;
-      const bool last = blk == p.nblocks - 1;
-      // ---- epilogue 1: h = lrelu(D1 + b1) -> XA buffer (all dilated-conv MMAs of the tile have retired)
-      mbar_wait(&bars.d1[kt - 1], ph);
-      tc_fence_after();
-      for (int t = 0; t < kt; ++t) {
-        for (int c = hf; c < nchunks; c += 2) {
-          float v[16];
-          tmem_ld16(tlane + t * cp + c * 16, v);
-          uint32_t w[8];
+      // Writes lrelu'd channels [c0, c0+CW) of sequence row tau (given as packed bf16 pairs) into XA, plus the
+      // mirror rows ReflectionPad1d of the next dilated conv will read.  Rows outside [0, L) are skipped.
+      auto put_xa = [&](int tau, const uint32_t* w) {
+        if (tau < 0 || tau >= L) return;
+        auto row_store = [&](int r) {             // r = staged row (0 = sequence row g0)
+          uint8_t* dst = xa + (size_t)(G + r) * 16;
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            w[i] = pack_bf16x2(lrelu_f(v[2 * i] + s_bias[blk][0][c * 16 + 2 * i], p.slope),
-                               lrelu_f(v[2 * i + 1] + s_bias[blk][0][c * 16 + 2 * i + 1], p.slope));
-          uint8_t* dst = sXA + (size_t)(2 * c) * plane_bytes + (size_t)(G + t * 128 + m) * 16;
-          *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
-          *reinterpret_cast<uint4*>(dst + plane_bytes) = make_uint4(w[4], w[5], w[6], w[7]);
+          for (int pl = 0; pl < CW / 8; ++pl)
+            *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) =
+                make_uint4(w[4 * pl], w[4 * pl + 1], w[4 * pl + 2], w[4 * pl + 3]);
+        };
+        row_store(tau - g0);
+        if (tau >= 1 && tau <= G && -tau - g0 >= -G) row_store(-tau - g0);
+        const int back = L - 1 - tau;
+        if (back >= 1 && back <= G && L - 1 + back - g0 < TR + G) row_store(L - 1 + back - g0);
+      };
+
+      // ---- prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place
+      mbar_wait_relaxed(&bars.x_full[buf], (it >> 1) & 1);
+      tr(200);
+      {
+        uint32_t w[CW / 2];
+        const uint8_t* src = xa + (size_t)(G + t * 128 + m) * 16;
+#pragma unroll
+        for (int pl = 0; pl < CW / 8; ++pl) {
+          const uint4 u = *reinterpret_cast<const uint4*>(src + (size_t)pl * plane_bytes);
+          w[4 * pl] = u.x; w[4 * pl + 1] = u.y; w[4 * pl + 2] = u.z; w[4 * pl + 3] = u.w;
         }
+        tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+#pragma unroll
+        for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
+        put_xa(g0 + t * 128 + m, w);
+        tmem_wait_st();
         fence_proxy_async();
-        mbar_arrive(&bars.h[t]);
+        tc_fence_before();
+        mbar_arrive(&bars.xa_ready[t]);
+        tr(201);
       }
-      // ---- epilogue 2: x_new = D2 + (b2 + bs)
-      for (int t = 0; t < kt; ++t) {
-        mbar_wait(&bars.d2[t], ph);
-        tc_fence_after();
-        const int tau = g0 + t * 128 + m;       // sequence row of this thread
-        const bool own = tau >= (int)blockIdx.x * V && tau < ((int)blockIdx.x + 1) * V && tau < p.L;
-        for (int c = hf; c < nchunks; c += 2) {
-          float v[16];
-          tmem_ld16(tlane + (kt + t) * cp + c * 16, v);
+
+      for (int blk = 0; blk < nb; ++blk, ++gb) {
+        const uint32_t ph = gb & 1;
+        const bool last = blk == nb - 1;
+        // ---- epilogue 1: h = lrelu(D1 + b1) -> bf16 over the low columns of D1 (A operand of the 1x1 conv)
+        {
+          mbar_wait_relaxed(&bars.d1_full[t], ph);
+          tc_fence_after();
+          tr(210);
+          uint32_t v[CW];
+          tmem_ld_nw<CW>(tlane + c0, v);
+          tmem_wait_ld();
+          tr(212);
+          uint32_t w[CW / 2];
+          const float4* bias = reinterpret_cast<const float4*>(&s_bias[blk][0][c0]);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] += s_bias[blk][1][c * 16 + i];
+          for (int i = 0; i < CW / 4; ++i) {
+            const float4 bv = bias[i];
+            w[2 * i] = pack_bf16x2(lrelu_f(__uint_as_float(v[4 * i]) + bv.x, slope),
+                                   lrelu_f(__uint_as_float(v[4 * i + 1]) + bv.y, slope));
+            w[2 * i + 1] = pack_bf16x2(lrelu_f(__uint_as_float(v[4 * i + 2]) + bv.z, slope),
+                                       lrelu_f(__uint_as_float(v[4 * i + 3]) + bv.w, slope));
+          }
+          // every warp of the quarter must have read D1 before any of them overwrites its low columns
+          tr(213);
+          if (CS > 1) asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "n"(CS * 32) : "memory");
+          tmem_st<CW / 2>(tlane + c0 / 2, w);
+          tmem_wait_st();
+          tr(214);
+          tc_fence_before();
+          mbar_arrive(&bars.h_ready[t]);
+          tr(211);
+        }
+        // ---- epilogue 2: x_new = D2 + (b2 + bs) -> XR[t] (raw) and XA (lrelu), or the stage output
+        {
+          mbar_wait_relaxed(&bars.d2_full[t], ph);
+          tc_fence_after();
+          tr(220);
+          uint32_t v[CW];
+          tmem_ld_nw<CW>(tlane + CP + c0, v);
+          tmem_wait_ld();
+          tr(223);
+          const int tau = g0 + t * 128 + m;
+          const float4* bias = reinterpret_cast<const float4*>(&s_bias[blk][1][c0]);
+          uint32_t w[CW / 2];
           if (!last) {
-            uint32_t w[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
-            const size_t off = (size_t)(2 * c) * plane_bytes + (size_t)(G + t * 128 + m) * 16;
-            *reinterpret_cast<uint4*>(sXR + off) = make_uint4(w[0], w[1], w[2], w[3]);
-            *reinterpret_cast<uint4*>(sXR + off + plane_bytes) = make_uint4(w[4], w[5], w[6], w[7]);
+            for (int i = 0; i < CW / 4; ++i) {
+              const float4 bv = bias[i];
+              w[2 * i] = pack_bf16x2(__uint_as_float(v[4 * i]) + bv.x, __uint_as_float(v[4 * i + 1]) + bv.y);
+              w[2 * i + 1] = pack_bf16x2(__uint_as_float(v[4 * i + 2]) + bv.z, __uint_as_float(v[4 * i + 3]) + bv.w);
+            }
+            tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) w[i] = lrelu_bf16x2(w[i], p.slope);
-            *reinterpret_cast<uint4*>(sXA + off) = make_uint4(w[0], w[1], w[2], w[3]);
-            *reinterpret_cast<uint4*>(sXA + off + plane_bytes) = make_uint4(w[4], w[5], w[6], w[7]);
-          } else if (own) {
-            canon_store16(p.out, b, c * 16, tau, v, p.slope);
+            for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
+            tr(224);
+            put_xa(tau, w);
+            tr(225);
+            tmem_wait_st();
+            fence_proxy_async();
+            tr(226);
+            tc_fence_before();
+            mbar_arrive(&bars.xa_ready[t]);
+            tr(221);
+          } else {
+            const bool own = tau >= chain * V && tau < (chain + 1) * V && tau < L;
+            if (own) {
+              const TcCanonOut& o = p.out;
+#pragma unroll
+              for (int i = 0; i < CW / 4; ++i) {
+                const float4 bv = bias[i];
+                float a0 = __uint_as_float(v[4 * i]) + bv.x, a1 = __uint_as_float(v[4 * i + 1]) + bv.y;
+                float a2 = __uint_as_float(v[4 * i + 2]) + bv.z, a3 = __uint_as_float(v[4 * i + 3]) + bv.w;
+                if (o.lrelu) {
+                  a0 = lrelu_f(a0, slope); a1 = lrelu_f(a1, slope); a2 = lrelu_f(a2, slope); a3 = lrelu_f(a3, slope);
+                }
+                w[2 * i] = pack_bf16x2(a0, a1);
+                w[2 * i + 1] = pack_bf16x2(a2, a3);
+              }
+              __nv_bfloat16* ob = o.base + (int64_t)b * o.batch_stride + (int64_t)(c0 / 8) * o.plane_rows * 8;
+              auto put = [&](int row, bool zero) {
+#pragma unroll
+                for (int pl = 0; pl < CW / 8; ++pl)
+                  *reinterpret_cast<uint4*>(ob + ((int64_t)pl * o.plane_rows + row) * 8) =
+                      zero ? make_uint4(0, 0, 0, 0) : make_uint4(w[4 * pl], w[4 * pl + 1], w[4 * pl + 2], w[4 * pl + 3]);
+              };
+              put(o.halo + tau, false);
+              if (o.margin == 1) {          // halo rows mirror the interior (ReflectionPad1d of the consumer)
+                if (tau >= 1 && tau <= o.halo) put(o.halo - tau, false);
+                const int back = o.L - 1 - tau;
+                if (back >= 1 && back <= o.halo) put(o.halo + o.L - 1 + back, false);
+              } else if (o.margin == 2) {   // zero rows either side (transposed conv of the consumer)
+                if (tau == 0) put(o.halo - 1, true);
+                if (tau == o.L - 1) put(o.halo + o.L, true);
+              }
+            }
+            tr(222);
           }
         }
-      }
-      if (!last) {
-        epi_barrier();
-        mirror(p.dil[blk + 1]);
-        fence_proxy_async();
-        mbar_arrive(&bars.xready);
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tbase, tcols);
+  if (warp == PRODUCER_WARP) tmem_dealloc(tbase, 512);
 }
 
-constexpr size_t SMEM_MAX = 227 * 1024 - 8 * 1024;   // static: barriers + bias table
+constexpr size_t SMEM_MAX = 227 * 1024 - 6 * 1024;   // static: barriers + bias table (<= 4*2*96*4 B)
+
+template <int CP, int KT, int CS>
+cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
+  auto kern = tc_stack_kernel<CP, KT, CS>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, 64 + KT * CS * 128, smem, stream>>>(p);
+  return cudaGetLastError();
+}
 
 }  // namespace
 
-size_t tc_stack_smem_bytes(const TcStackParams& p) {
-  const size_t RS = (size_t)p.kt * 128 + 2 * p.guard;
-  return 2 * (size_t)(p.cp / 8) * RS * 16 + (size_t)(p.res_taps + 2) * p.cp * p.cp * 2;
+int tc_stack_kt(int cp) {
+  switch (cp) {
+    case 96: return 2;
+    case 64: return 3;
+    case 48: return 4;
+    case 32: return 4;
+    default: return 0;
+  }
 }
 
-cudaError_t tc_stack_launch(const TcStackParams& p, int batch, cudaStream_t stream) {
+// Fills kt / guard / w_sets for a stage (cp, dilations, nblocks set by the caller); returns false when the
+// stage cannot run on the fused kernel.
+bool tc_stack_configure(TcStackParams& p) {
+  p.kt = tc_stack_kt(p.cp);
+  if (p.kt == 0 || p.res_taps != TAPS || p.nblocks < 1 || p.nblocks > TC_STACK_MAX_BLOCKS) return false;
+  int dmax = 1;
+  p.sum_d = 0;
+  for (int i = 0; i < p.nblocks; ++i) {
+    p.sum_d += p.dil[i];
+    dmax = dmax > p.dil[i] ? dmax : p.dil[i];
+  }
+  p.guard = (dmax + 7) / 8 * 8;
+  if (p.kt * 128 - 2 * p.sum_d < 32 || p.guard + p.sum_d > 127) return false;
+  const size_t xa = 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;
+  const size_t wset = (size_t)(TAPS + 2) * p.cp * p.cp * 2;
+  if (xa + wset > SMEM_MAX) return false;
+  p.w_sets = xa + p.nblocks * wset <= SMEM_MAX ? p.nblocks : 1;
+  return true;
+}
+
+cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream);
+
+size_t tc_stack_smem_bytes(const TcStackParams& p) {
+  return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2;
+}
+
+cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t stream) {
+  TcStackParams p = p_in;
+  if (p.kt != tc_stack_kt(p.cp) || p.kt == 0) return cudaErrorInvalidConfiguration;
   const size_t smem = tc_stack_smem_bytes(p);
-  if (smem > SMEM_MAX || p.cp > 96 || p.cp % 16 || p.kt < 1 || p.kt > TC_STACK_MAX_KT ||
-      p.nblocks < 1 || p.nblocks > TC_STACK_MAX_BLOCKS || 2 * p.kt * p.cp > 512)
-    return cudaErrorInvalidConfiguration;
-  cudaError_t e = cudaFuncSetAttribute(tc_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-  if (e != cudaSuccess) return e;
+  if (smem > SMEM_MAX) return cudaErrorInvalidConfiguration;
   const int V = p.kt * 128 - 2 * p.sum_d;
-  const dim3 grid(ceil_div(p.L, V), batch);
-  tc_stack_kernel<<<grid, NT, smem, stream>>>(p);
-  return cudaGetLastError();
+  p.batch = batch;
+  p.n_chains = ceil_div(p.L, V);
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int items = p.n_chains * batch;
+  const int grid = items < sms ? items : sms;
+  const char* trace_path = getenv("TTSB200_STACK_TRACE");
+  if (trace_path) {
+    cudaMalloc(&p.trace, 8 * 256 * sizeof(long long));
+    cudaMemsetAsync(p.trace, 0, 8 * 256 * sizeof(long long), stream);
+  }
+  cudaError_t rc = dispatch(p, smem, grid, stream);
+  if (trace_path && rc == cudaSuccess) {
+    std::vector<long long> h(8 * 256);
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(h.data(), p.trace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaFree(p.trace);
+    if (FILE* f = fopen(trace_path, "a")) {
+      for (int r = 0; r < 8; ++r)
+        for (int i = 0; i < 256 && h[r * 256 + i]; i += 2)
+          fprintf(f, "%d %d %d %lld\n", p.cp, r, (int)h[r * 256 + i], h[r * 256 + i + 1]);
+      fclose(f);
+    }
+  }
+  return rc;
+}
+
+cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
+  switch (p.cp) {
+    case 96: return launch<96, 2, 2>(p, smem, grid, stream);
+    case 64: return launch<64, 3, 1>(p, smem, grid, stream);
+    case 48: return launch<48, 4, 1>(p, smem, grid, stream);
+    case 32: return launch<32, 4, 1>(p, smem, grid, stream);
+    default: return cudaErrorInvalidConfiguration;
+  }
 }
 
 }  // namespace ttsb

@@ -72,7 +72,7 @@ struct TcCanonOut {
 };
 
 // Fused ResidualStack (melgan.py:36-39): x <- S_b x + W2_b lrelu(W1_b * lrelu(x)) for b = 0..n-1 in ONE
-// kernel, activations resident in shared memory, accumulators in TMEM.
+// persistent kernel: lrelu(x) in shared memory, raw x / h / accumulators in TMEM (stack_bf16_tc.cu).
 constexpr int TC_STACK_MAX_BLOCKS = 4;
 constexpr int TC_STACK_MAX_KT = 4;
 struct TcStackParams {
@@ -88,12 +88,17 @@ struct TcStackParams {
   const __nv_bfloat16* w2s[TC_STACK_MAX_BLOCKS];  // [2][cp/8][cp][8]  (conv 1x1, shortcut 1x1)
   const float* b1[TC_STACK_MAX_BLOCKS];           // [cp]
   const float* b2s[TC_STACK_MAX_BLOCKS];          // [cp]  conv2.bias + shortcut.bias
-  int kt;                  // 128-row M tiles per CTA
-  int sum_d;               // one-sided receptive field of the stack = sum over blocks of half*dil
+  int kt;                  // 128-row M tiles per work item (fixed per cp: tc_stack_kt)
+  int sum_d;               // one-sided receptive field of the stack = sum over blocks of dil
   int guard;               // spare rows either side of the staged tile (>= max dilation reach)
+  int w_sets;              // nblocks: all weights resident in shared memory; 1: streamed per block
+  int batch, n_chains;     // filled by tc_stack_launch: work items = batch x n_chains
+  long long* trace;        // optional (TTSB200_STACK_TRACE): [role][256] {tag, clock} pairs written by CTA 0
   TcCanonOut out;
   float slope;
 };
+int tc_stack_kt(int cp);                          // 0: this channel count has no fused kernel
+bool tc_stack_configure(TcStackParams& p);        // fills kt / sum_d / guard / w_sets from cp, dil[], nblocks
 size_t tc_stack_smem_bytes(const TcStackParams& p);
 cudaError_t tc_stack_launch(const TcStackParams& p, int batch, cudaStream_t stream);
 

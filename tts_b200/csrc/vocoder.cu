@@ -86,6 +86,8 @@ int validate_cfg(const ttsb200_generator_config& c) {
   if (c.pqmf_bands < 0 || (c.pqmf_bands > 0 && c.pqmf_bands != c.out_channels))
     return fail(TTSB200_ERR_INVALID, "pqmf_bands must equal out_channels");
   if (c.pqmf_bands > 0 && c.pqmf_taps <= 0) return fail(TTSB200_ERR_INVALID, "pqmf_taps must be positive");
+  if (!(c.act_slope >= 0.f && c.act_slope <= 1.f))   // kernels use lrelu(v) = max(v, slope v)
+    return fail(TTSB200_ERR_INVALID, "act_slope must be in [0, 1]");
   return 0;
 }
 
