@@ -7,7 +7,8 @@
 //   XA   (shared, canonical [CP/8][RS][8] bf16, double-buffered across items)  lrelu(x): A operand of the
 //        dilated conv — each tap is the same tile at a different start row, so only the descriptor moves;
 //   XR[t] (TMEM, bf16, CP/2 columns)  raw x of tile t: A operand of the 1x1 shortcut (A-from-TMEM MMA);
-//   D1[t] (TMEM, fp32, CP columns)    dilated-conv accumulator; its epilogue writes h = lrelu(D1 + b1) as bf16
+//   D1[t] (TMEM, fp32, CP columns)    dilated-conv accumulator, pre-loaded with the bias row by tcgen05.st so the
+//        epilogue has no bias add; its epilogue writes h = lrelu(D1 + b1) as bf16
 //        over the low CP/2 columns of the same region -> A operand of the 1x1 conv, never touching smem;
 //   D2[t] (TMEM, fp32, CP columns)    W2 h + S x accumulator = x of the next block.
 //   W1 / W2S (shared)  weights of the current block, or of all blocks when they fit (then loaded once per CTA).
@@ -47,6 +48,7 @@ constexpr int MAX_KT = TC_STACK_MAX_KT;
 
 // Timeline capture for CTA 0 (debug aid, enabled by TTSB200_STACK_TRACE=<file>): role r appends {tag, clock64}.
 #ifdef TTSB_STACK_TRACE
+#define DBG(bit) (p.debug & (bit))
 struct Tracer {
   long long* buf;
   int n;
@@ -61,7 +63,9 @@ struct Tracer {
 __device__ __forceinline__ Tracer make_tracer(const TcStackParams& p, int role, bool leader) {
   return Tracer{(p.trace && blockIdx.x == 0 && leader) ? p.trace + role * 256 : nullptr, 0};
 }
-#else   // compiled out: the trace points cost instruction-cache space in a kernel that is sensitive to it
+#else
+#define DBG(bit) false
+// compiled out: the trace points cost instruction-cache space in a kernel that is sensitive to it
 struct Tracer {
   __device__ __forceinline__ void operator()(int) {}
 };
@@ -208,7 +212,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
 #pragma unroll
                 for (int kk = 0; kk < KS; ++kk)
                   umma_bf16(dcol, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
-                            b_tmpl | (uint64_t)((w_tap + 2 * kk * LBO_B) >> 4), idesc, (j | kk) != 0);
+                            b_tmpl | (uint64_t)((w_tap + 2 * kk * LBO_B) >> 4), idesc, 1);
               }
               umma_commit(&bars.d1_full[t]);
             }
@@ -232,7 +236,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
             if (leader) {
 #pragma unroll
               for (int kk = 0; kk < KS; ++kk)
-                umma_bf16_ts(tcol + CP, tcol + 8 * kk, b_tmpl | (uint64_t)((w2 + 2 * kk * LBO_B) >> 4), idesc, kk != 0);
+                umma_bf16_ts(tcol + CP, tcol + 8 * kk, b_tmpl | (uint64_t)((w2 + 2 * kk * LBO_B) >> 4), idesc, 1);
 #pragma unroll
               for (int kk = 0; kk < KS; ++kk)
                 umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
@@ -269,24 +273,46 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
       const int g0 = chain * V - p.sum_d;       // sequence row of staged row 0
       uint8_t* xa = sXA + (size_t)buf * xa_bytes + (size_t)(c0 / 8) * plane_bytes;   // this thread's first plane
 
-      // Writes lrelu'd channels [c0, c0+CW) of sequence row tau (given as packed bf16 pairs) into XA, plus the
-      // mirror rows ReflectionPad1d of the next dilated conv will read.  Rows outside [0, L) are skipped.
-      auto put_xa = [&](int tau, const uint32_t* w) {
-        if (tau < 0 || tau >= L) return;
-        auto row_store = [&](int r) {             // r = staged row (0 = sequence row g0)
-          uint8_t* dst = xa + (size_t)(G + r) * 16;
+      // Items whose staged rows stay clear of both sequence ends take the unconditional store path.
+      const int reach = G > p.out.halo ? G : p.out.halo;   // mirror rows: `guard` in XA, `halo` in the output
+      const bool edge = g0 <= reach || g0 + TR + reach >= L - 1;
+      // Writes lrelu'd channels [c0, c0+CW) of this thread's row (packed bf16 pairs) into XA.  Near a sequence
+      // end: rows outside [0, L) are skipped and rows within `guard` of the end are also written to their mirror
+      // position (what ReflectionPad1d of the next dilated conv reads).
+      auto row_store = [&](int r, const uint32_t* w) {      // r = staged row (0 = sequence row g0)
+        if (DBG(1)) return;
+        uint8_t* dst = xa + (size_t)(G + r) * 16;
 #pragma unroll
-          for (int pl = 0; pl < CW / 8; ++pl)
-            *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) =
-                make_uint4(w[4 * pl], w[4 * pl + 1], w[4 * pl + 2], w[4 * pl + 3]);
-        };
-        row_store(tau - g0);
-        if (tau >= 1 && tau <= G && -tau - g0 >= -G) row_store(-tau - g0);
+        for (int pl = 0; pl < CW / 8; ++pl)
+          *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) =
+              make_uint4(w[4 * pl], w[4 * pl + 1], w[4 * pl + 2], w[4 * pl + 3]);
+      };
+      auto put_xa = [&](const uint32_t* w) {
+        if (!edge) {
+          row_store(t * 128 + m, w);
+          return;
+        }
+        const int tau = g0 + t * 128 + m;
+        if (tau < 0 || tau >= L) return;
+        row_store(tau - g0, w);
+        if (tau >= 1 && tau <= G && -tau - g0 >= -G) row_store(-tau - g0, w);
         const int back = L - 1 - tau;
-        if (back >= 1 && back <= G && L - 1 + back - g0 < TR + G) row_store(L - 1 + back - g0);
+        if (back >= 1 && back <= G && L - 1 + back - g0 < TR + G) row_store(L - 1 + back - g0, w);
+      };
+      // Accumulators start from the bias: D[t] <- bias row, then every MMA accumulates (no FADD in the epilogues).
+      auto init_acc = [&](uint32_t taddr, const float* bias_row) {
+        uint32_t bv[CW];
+        const float4* src = reinterpret_cast<const float4*>(bias_row + c0);
+#pragma unroll
+        for (int i = 0; i < CW / 4; ++i) {
+          const float4 f = src[i];
+          bv[4 * i] = __float_as_uint(f.x); bv[4 * i + 1] = __float_as_uint(f.y);
+          bv[4 * i + 2] = __float_as_uint(f.z); bv[4 * i + 3] = __float_as_uint(f.w);
+        }
+        tmem_st<CW>(taddr + c0, bv);
       };
 
-      // ---- prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place
+      // ---- prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place; accumulators <- block 0 biases
       mbar_wait_relaxed(&bars.x_full[buf], (it >> 1) & 1);
       tr(200);
       {
@@ -298,9 +324,11 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
           w[4 * pl] = u.x; w[4 * pl + 1] = u.y; w[4 * pl + 2] = u.z; w[4 * pl + 3] = u.w;
         }
         tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+        init_acc(tlane, s_bias[0][0]);
+        init_acc(tlane + CP, s_bias[0][1]);
 #pragma unroll
         for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
-        put_xa(g0 + t * 128 + m, w);
+        put_xa(w);
         tmem_wait_st();
         fence_proxy_async();
         tc_fence_before();
@@ -311,7 +339,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
       for (int blk = 0; blk < nb; ++blk, ++gb) {
         const uint32_t ph = gb & 1;
         const bool last = blk == nb - 1;
-        // ---- epilogue 1: h = lrelu(D1 + b1) -> bf16 over the low columns of D1 (A operand of the 1x1 conv)
+        // ---- epilogue 1: h = lrelu(D1) -> bf16 over the low columns of D1 (A operand of the 1x1 conv)
         {
           mbar_wait_relaxed(&bars.d1_full[t], ph);
           tc_fence_after();
@@ -321,26 +349,20 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
           tmem_wait_ld();
           tr(212);
           uint32_t w[CW / 2];
-          const float4* bias = reinterpret_cast<const float4*>(&s_bias[blk][0][c0]);
 #pragma unroll
-          for (int i = 0; i < CW / 4; ++i) {
-            const float4 bv = bias[i];
-            w[2 * i] = pack_bf16x2(lrelu_f(__uint_as_float(v[4 * i]) + bv.x, slope),
-                                   lrelu_f(__uint_as_float(v[4 * i + 1]) + bv.y, slope));
-            w[2 * i + 1] = pack_bf16x2(lrelu_f(__uint_as_float(v[4 * i + 2]) + bv.z, slope),
-                                       lrelu_f(__uint_as_float(v[4 * i + 3]) + bv.w, slope));
-          }
-          // every warp of the quarter must have read D1 before any of them overwrites its low columns
+          for (int i = 0; i < CW / 2; ++i)
+            w[i] = pack_bf16x2(lrelu_f(__uint_as_float(v[2 * i]), slope), lrelu_f(__uint_as_float(v[2 * i + 1]), slope));
           tr(213);
+          // every warp of the quarter must have read D1 before any of them overwrites its low columns
           if (CS > 1) asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "n"(CS * 32) : "memory");
-          tmem_st<CW / 2>(tlane + c0 / 2, w);
+          if (!DBG(2)) tmem_st<CW / 2>(tlane + c0 / 2, w);
           tmem_wait_st();
           tr(214);
           tc_fence_before();
           mbar_arrive(&bars.h_ready[t]);
           tr(211);
         }
-        // ---- epilogue 2: x_new = D2 + (b2 + bs) -> XR[t] (raw) and XA (lrelu), or the stage output
+        // ---- epilogue 2: x_new = D2 -> XR[t] (raw) and XA (lrelu), or the stage output
         {
           mbar_wait_relaxed(&bars.d2_full[t], ph);
           tc_fence_after();
@@ -349,42 +371,37 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
           tmem_ld_nw<CW>(tlane + CP + c0, v);
           tmem_wait_ld();
           tr(223);
-          const int tau = g0 + t * 128 + m;
-          const float4* bias = reinterpret_cast<const float4*>(&s_bias[blk][1][c0]);
           uint32_t w[CW / 2];
           if (!last) {
+            // the 1x1 MMAs of this tile have retired: both accumulators may take the next block's biases
+            init_acc(tlane, s_bias[blk + 1][0]);
+            init_acc(tlane + CP, s_bias[blk + 1][1]);
 #pragma unroll
-            for (int i = 0; i < CW / 4; ++i) {
-              const float4 bv = bias[i];
-              w[2 * i] = pack_bf16x2(__uint_as_float(v[4 * i]) + bv.x, __uint_as_float(v[4 * i + 1]) + bv.y);
-              w[2 * i + 1] = pack_bf16x2(__uint_as_float(v[4 * i + 2]) + bv.z, __uint_as_float(v[4 * i + 3]) + bv.w);
-            }
-            tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+            for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+            if (!DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
             tr(224);
-            put_xa(tau, w);
+            put_xa(w);
             tr(225);
             tmem_wait_st();
-            fence_proxy_async();
+            if (!DBG(8)) fence_proxy_async();
             tr(226);
             tc_fence_before();
             mbar_arrive(&bars.xa_ready[t]);
             tr(221);
           } else {
+            const int tau = g0 + t * 128 + m;
             const bool own = tau >= chain * V && tau < (chain + 1) * V && tau < L;
             if (own) {
               const TcCanonOut& o = p.out;
+              if (o.lrelu) {
 #pragma unroll
-              for (int i = 0; i < CW / 4; ++i) {
-                const float4 bv = bias[i];
-                float a0 = __uint_as_float(v[4 * i]) + bv.x, a1 = __uint_as_float(v[4 * i + 1]) + bv.y;
-                float a2 = __uint_as_float(v[4 * i + 2]) + bv.z, a3 = __uint_as_float(v[4 * i + 3]) + bv.w;
-                if (o.lrelu) {
-                  a0 = lrelu_f(a0, slope); a1 = lrelu_f(a1, slope); a2 = lrelu_f(a2, slope); a3 = lrelu_f(a3, slope);
-                }
-                w[2 * i] = pack_bf16x2(a0, a1);
-                w[2 * i + 1] = pack_bf16x2(a2, a3);
+                for (int i = 0; i < CW / 2; ++i)
+                  w[i] = pack_bf16x2(lrelu_f(__uint_as_float(v[2 * i]), slope), lrelu_f(__uint_as_float(v[2 * i + 1]), slope));
+              } else {
+#pragma unroll
+                for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
               }
               __nv_bfloat16* ob = o.base + (int64_t)b * o.batch_stride + (int64_t)(c0 / 8) * o.plane_rows * 8;
               auto put = [&](int row, bool zero) {
@@ -394,13 +411,15 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
                       zero ? make_uint4(0, 0, 0, 0) : make_uint4(w[4 * pl], w[4 * pl + 1], w[4 * pl + 2], w[4 * pl + 3]);
               };
               put(o.halo + tau, false);
-              if (o.margin == 1) {          // halo rows mirror the interior (ReflectionPad1d of the consumer)
-                if (tau >= 1 && tau <= o.halo) put(o.halo - tau, false);
-                const int back = o.L - 1 - tau;
-                if (back >= 1 && back <= o.halo) put(o.halo + o.L - 1 + back, false);
-              } else if (o.margin == 2) {   // zero rows either side (transposed conv of the consumer)
-                if (tau == 0) put(o.halo - 1, true);
-                if (tau == o.L - 1) put(o.halo + o.L, true);
+              if (edge) {
+                if (o.margin == 1) {          // halo rows mirror the interior (ReflectionPad1d of the consumer)
+                  if (tau >= 1 && tau <= o.halo) put(o.halo - tau, false);
+                  const int back = o.L - 1 - tau;
+                  if (back >= 1 && back <= o.halo) put(o.halo + o.L - 1 + back, false);
+                } else if (o.margin == 2) {   // zero rows either side (transposed conv of the consumer)
+                  if (tau == 0) put(o.halo - 1, true);
+                  if (tau == o.L - 1) put(o.halo + o.L, true);
+                }
               }
             }
             tr(222);
@@ -477,6 +496,7 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
   const int items = p.n_chains * batch;
   const int grid = items < sms ? items : sms;
   const char* trace_path = getenv("TTSB200_STACK_TRACE");
+  if (const char* dbg = getenv("TTSB200_STACK_DEBUG")) p.debug = atoi(dbg);
   if (trace_path) {
     cudaMalloc(&p.trace, 8 * 256 * sizeof(long long));
     cudaMemsetAsync(p.trace, 0, 8 * 256 * sizeof(long long), stream);

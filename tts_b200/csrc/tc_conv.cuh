@@ -93,6 +93,7 @@ struct TcStackParams {
   int guard;               // spare rows either side of the staged tile (>= max dilation reach)
   int w_sets;              // nblocks: all weights resident in shared memory; 1: streamed per block
   int batch, n_chains;     // filled by tc_stack_launch: work items = batch x n_chains
+  int debug;               // knock-out bits for timeline experiments (trace builds only)
   long long* trace;        // optional (TTSB200_STACK_TRACE): [role][256] {tag, clock} pairs written by CTA 0
   TcCanonOut out;
   float slope;
