@@ -25,11 +25,12 @@ namespace {
 
 constexpr int NT = 192;
 
-__global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcConvParams p, const int w_stage_bytes,
+__global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcConvParams p, const int kb_stage,
                                                       const int nst) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bar_a, bar_a_ready, bar_d, bar_full[TC_STAGES], bar_empty[TC_STAGES];
+  __shared__ __align__(8) uint64_t bar_a, bar_a_ready, bar_d, bar_full[TC_MAX_STAGES], bar_empty[TC_MAX_STAGES];
   __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float s_bias[256];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int t0 = blockIdx.x * TC_TILE_M;
@@ -39,6 +40,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
 
   const uint32_t a_bytes0 = (uint32_t)p.src[0].planes * p.src[0].rows * 16;
   const uint32_t a_bytes1 = p.nsrc > 1 ? (uint32_t)p.src[1].planes * p.src[1].rows * 16 : 0;
+  const uint32_t w_stage_bytes = (uint32_t)(kb_stage / 8) * ncols * 16;
   uint8_t* sA0 = smem;
   uint8_t* sA1 = smem + a_bytes0;
   uint8_t* sW = smem + a_bytes0 + a_bytes1;
@@ -58,6 +60,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc(&tmem_base_s, tcols);
+  for (int c = tid; c < ncols; c += NT) s_bias[c] = G.bias[c];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -81,8 +84,8 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
       for (int s = 0; s < p.nsrc; ++s) {
         const int cp = p.src[s].planes * 8;
         for (int j = 0; j < p.src[s].taps; ++j)
-          for (int c0 = 0; c0 < cp; c0 += TC_KB, ++it) {
-            const int kb = min(TC_KB, cp - c0);
+          for (int c0 = 0; c0 < cp; c0 += kb_stage, ++it) {
+            const int kb = min(kb_stage, cp - c0);
             const int st = it % nst;
             const uint32_t ph = (it / nst) & 1;
             mbar_wait(&bar_empty[st], ph ^ 1);
@@ -94,39 +97,47 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
       }
     }
   } else if (warp == 1) {
-    if (elect_one()) {
-      if (need_lrelu) mbar_wait(&bar_a_ready, 0); else mbar_wait(&bar_a, 0);
-      tc_fence_after();
-      const uint32_t idesc = make_idesc_bf16(TC_TILE_M, ncols);
-      const uint32_t lbo_b = (uint32_t)ncols * 16;
-      int it = 0;
-      uint32_t acc = 0;
-      for (int s = 0; s < p.nsrc; ++s) {
-        const TcSrc& S = p.src[s];
-        const int cp = S.planes * 8;
-        const uint32_t lbo_a = (uint32_t)S.rows * 16;
-        const uint32_t a_base = smem_u32(s ? sA1 : sA0);
-        for (int j = 0; j < S.taps; ++j) {
-          const uint32_t a_tap = a_base + (uint32_t)(S.tap_row[j] + G.tap_shift) * 16;
-          for (int c0 = 0; c0 < cp; c0 += TC_KB, ++it) {
-            const int kb = min(TC_KB, cp - c0);
-            const int st = it % nst;
-            const uint32_t ph = (it / nst) & 1;
-            mbar_wait(&bar_full[st], ph);
-            tc_fence_after();
-            const uint32_t w_base = smem_u32(sW + (size_t)st * w_stage_bytes);
+    // ---- MMA issuer: the whole warp walks the loops (addresses stay in uniform registers), one lane issues
+    const bool leader = elect_one() != 0;
+    if (need_lrelu) mbar_wait(&bar_a_ready, 0); else mbar_wait(&bar_a, 0);
+    tc_fence_after();
+    const uint32_t idesc = make_idesc_bf16(TC_TILE_M, ncols);
+    const uint32_t lbo_b = (uint32_t)ncols * 16;
+    const uint64_t b_tmpl = make_desc(0, lbo_b, 128);
+    int it = 0;
+    uint32_t acc = 0;
+    for (int s = 0; s < p.nsrc; ++s) {
+      const TcSrc& S = p.src[s];
+      const int cp = S.planes * 8;
+      const uint32_t lbo_a = (uint32_t)S.rows * 16;
+      const uint64_t a_tmpl = make_desc(0, lbo_a, 128);
+      const uint32_t a_base = smem_u32(s ? sA1 : sA0);
+      for (int j = 0; j < S.taps; ++j) {
+        const uint32_t a_tap = a_base + (uint32_t)S.tap_row[j] * 16;
+        for (int c0 = 0; c0 < cp; c0 += kb_stage, ++it) {
+          const int kb = min(kb_stage, cp - c0);
+          const int st = it % nst;
+          const uint32_t ph = (it / nst) & 1;
+          mbar_wait(&bar_full[st], ph);
+          tc_fence_after();
+          if (leader) {
+            uint32_t a_lo = (a_tap + (uint32_t)(c0 >> 3) * lbo_a) >> 4;
+            uint32_t b_lo = smem_u32(sW + (size_t)st * w_stage_bytes) >> 4;
             for (int kk = 0; kk < kb / 16; ++kk) {
-              const uint64_t ad = make_desc(a_tap + (uint32_t)((c0 >> 3) + 2 * kk) * lbo_a, lbo_a, 128);
-              const uint64_t bd = make_desc(w_base + (uint32_t)(2 * kk) * lbo_b, lbo_b, 128);
-              umma_bf16(tbase, ad, bd, idesc, acc);
+              umma_bf16(tbase, a_tmpl | a_lo, b_tmpl | b_lo, idesc, acc);
               acc = 1;
+              a_lo += lbo_a >> 3;   // two planes further, in 16-byte units
+              b_lo += lbo_b >> 3;
             }
             umma_commit(&bar_empty[st]);  // frees the stage once these MMAs have read it
           }
+          acc = 1;
+          __syncwarp();
         }
       }
-      umma_commit(&bar_d);
     }
+    if (leader) umma_commit(&bar_d);
+    __syncwarp();
   } else {
     // ---- warps 2..5: optional LeakyReLU over the staged tile, then the epilogue
     const int et = tid - 64;
@@ -147,61 +158,61 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
       fence_proxy_async();
       mbar_arrive(&bar_a_ready);
     }
-    mbar_wait(&bar_d, 0);
+    mbar_wait_relaxed(&bar_d, 0);
     tc_fence_after();
     const int q4 = warp & 3;                 // TMEM lane quarter this warp may read
-    const int m = q4 * 32 + lane;
-    const int t = t0 + m;
-    const bool row_ok = t < p.Lt;
+    const int q = t0 + q4 * 32 + lane;       // GEMM row of this thread
+    const bool row_ok = q < p.Lt;
     const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
-    for (int c = 0; c < ncols; c += 16) {
-      float v[16];
-      tmem_ld16(trow + c, v);
-      const int flat = G.ch_first + c;
-      const int r = G.phase_first + flat / p.cout_pad;
-      const int ch = flat % p.cout_pad;
-      const int tau = t * p.up_f + r;
-      if (!row_ok || tau >= p.out_L) continue;
+    const int f = p.up_f;
+    const int row0 = q * f - p.up_P;         // output row of phase 0
+    __nv_bfloat16* ob = p.out_c + (int64_t)b * p.out_batch_stride;
+    for (int c = 0; c < ncols; c += 32) {
+      const int nc = min(32, ncols - c);     // 16 or 32
+      uint32_t v[32];
+      tmem_ld16_nw(trow + c, v);
+      if (nc > 16) tmem_ld16_nw(trow + c + 16, v + 16);
+      tmem_wait_ld();
+      if (!row_ok) continue;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] += __ldg(G.bias + c + i);
-      if (p.out_mode == 0) {
-        if (p.out_lrelu) {
+      for (int u = 0; u < 4; ++u) {          // 8-column units: one (plane, phase) each
+        if (u * 8 >= nc) break;
+        const int unit = ((G.col_first + c) >> 3) + u;
+        const int plane = unit / f, r = unit - plane * f;
+        const int tau = row0 + r;
+        if (tau < 0 || tau >= p.out_L) continue;
+        const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[c + u * 8]);
+        const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[c + u * 8 + 4]);
+        float y[8];
+        y[0] = __uint_as_float(v[u * 8 + 0]) + b0.x; y[1] = __uint_as_float(v[u * 8 + 1]) + b0.y;
+        y[2] = __uint_as_float(v[u * 8 + 2]) + b0.z; y[3] = __uint_as_float(v[u * 8 + 3]) + b0.w;
+        y[4] = __uint_as_float(v[u * 8 + 4]) + b1.x; y[5] = __uint_as_float(v[u * 8 + 5]) + b1.y;
+        y[6] = __uint_as_float(v[u * 8 + 6]) + b1.z; y[7] = __uint_as_float(v[u * 8 + 7]) + b1.w;
+        if (p.out_mode == 0) {
+          if (p.out_lrelu) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = lrelu_f(v[i], p.slope);
-        }
-        uint4 lo, hi;
-        lo.x = pack_bf16x2(v[0], v[1]);   lo.y = pack_bf16x2(v[2], v[3]);
-        lo.z = pack_bf16x2(v[4], v[5]);   lo.w = pack_bf16x2(v[6], v[7]);
-        hi.x = pack_bf16x2(v[8], v[9]);   hi.y = pack_bf16x2(v[10], v[11]);
-        hi.z = pack_bf16x2(v[12], v[13]); hi.w = pack_bf16x2(v[14], v[15]);
-        __nv_bfloat16* ob = p.out_c + (int64_t)b * p.out_batch_stride;
-        const int64_t pl0 = (int64_t)(ch >> 3) * p.out_plane_rows;
-        const int64_t pl1 = pl0 + p.out_plane_rows;
-        auto put = [&](int row) {
-          *reinterpret_cast<uint4*>(ob + (pl0 + row) * 8) = lo;
-          *reinterpret_cast<uint4*>(ob + (pl1 + row) * 8) = hi;
-        };
-        put(p.out_halo + tau);
-        if (p.margin == 1) {           // halo rows mirror the interior (ReflectionPad1d of the consumer)
-          if (tau >= 1 && tau <= p.out_halo) put(p.out_halo - tau);
-          const int back = p.out_L - 1 - tau;
-          if (back >= 1 && back <= p.out_halo) put(p.out_halo + p.out_L - 1 + back);
-        } else if (p.margin == 2) {    // zero rows either side (transposed conv of the consumer)
-          const uint4 z = make_uint4(0, 0, 0, 0);
-          if (tau == 0) {
-            *reinterpret_cast<uint4*>(ob + (pl0 + p.out_halo - 1) * 8) = z;
-            *reinterpret_cast<uint4*>(ob + (pl1 + p.out_halo - 1) * 8) = z;
+            for (int i = 0; i < 8; ++i) y[i] = lrelu_f(y[i], p.slope);
           }
-          if (tau == p.out_L - 1) {
-            *reinterpret_cast<uint4*>(ob + (pl0 + p.out_halo + p.out_L) * 8) = z;
-            *reinterpret_cast<uint4*>(ob + (pl1 + p.out_halo + p.out_L) * 8) = z;
+          const uint4 w4 = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
+                                      pack_bf16x2(y[6], y[7]));
+          __nv_bfloat16* pb = ob + (int64_t)plane * p.out_plane_rows * 8;
+          *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo + tau) * 8) = w4;
+          if (p.margin == 1) {           // halo rows mirror the interior (ReflectionPad1d of the consumer)
+            if (tau >= 1 && tau <= p.out_halo) *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo - tau) * 8) = w4;
+            const int back = p.out_L - 1 - tau;
+            if (back >= 1 && back <= p.out_halo)
+              *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo + p.out_L - 1 + back) * 8) = w4;
+          } else if (p.margin == 2) {    // zero rows either side (transposed conv of the consumer)
+            const uint4 z = make_uint4(0, 0, 0, 0);
+            if (tau == 0) *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo - 1) * 8) = z;
+            if (tau == p.out_L - 1) *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo + p.out_L) * 8) = z;
           }
-        }
-      } else {
-        float* of = p.out_f + ((int64_t)b * p.cout_real + ch) * p.out_L + tau;
+        } else {
+          float* of = p.out_f + ((int64_t)b * p.cout_real + plane * 8) * p.out_L + tau;
 #pragma unroll
-        for (int i = 0; i < 16; ++i)
-          if (ch + i < p.cout_real) of[(int64_t)i * p.out_L] = tanhf(v[i]);
+          for (int i = 0; i < 8; ++i)
+            if (plane * 8 + i < p.cout_real) of[(int64_t)i * p.out_L] = tanhf(y[i]);
+        }
       }
     }
   }
@@ -249,26 +260,33 @@ __global__ void untile_kernel(const __nv_bfloat16* __restrict__ x, int C, int64_
 }  // namespace
 
 namespace {
-constexpr size_t SMEM_MAX = 227 * 1024 - 1024;  // static barriers live in the same 227 KB
-struct SmemPlan { size_t a_bytes; int w_stage_bytes, nst; };
+constexpr size_t SMEM_MAX = 227 * 1024 - 3 * 1024;     // static barriers + bias table live in the same 227 KB
+constexpr size_t SMEM_HALF = 113 * 1024 - 3 * 1024;    // budget that lets two CTAs share an SM
+struct SmemPlan { size_t a_bytes, total; int kb_stage, nst; };
+// Weight ring geometry: the deepest / widest ring that still lets two CTAs share an SM (their loads, MMAs and
+// epilogues then overlap); if the activation tile alone is too big for that, the best ring that fits at all.
 SmemPlan smem_plan(const TcConvParams& p) {
   SmemPlan s{};
   s.a_bytes = (size_t)p.src[0].planes * p.src[0].rows * 16;
   if (p.nsrc > 1) s.a_bytes += (size_t)p.src[1].planes * p.src[1].rows * 16;
   int nmax = 0;
   for (int g = 0; g < p.ngroups; ++g) nmax = nmax > p.grp[g].ncols ? nmax : p.grp[g].ncols;
-  s.w_stage_bytes = (TC_KB / 8) * nmax * 16;
-  s.nst = TC_STAGES;
-  while (s.nst > 2 && s.a_bytes + (size_t)s.nst * s.w_stage_bytes > SMEM_MAX) --s.nst;
+  static const int opts[][2] = {{64, 4}, {64, 3}, {32, 4}, {32, 3}, {32, 2}, {16, 3}, {16, 2}};
+  for (size_t budget : {SMEM_HALF, SMEM_MAX})
+    for (auto& o : opts) {
+      const size_t tot = s.a_bytes + (size_t)o[1] * (o[0] / 8) * nmax * 16;
+      if (tot <= budget) {
+        s.kb_stage = o[0]; s.nst = o[1]; s.total = tot;
+        return s;
+      }
+    }
+  s.total = (size_t)-1;
   return s;
 }
 }  // namespace
 
-// bytes of dynamic shared memory of the launch (deepest weight ring, 3 down to 2 stages, that fits)
-size_t tc_conv_smem_bytes(const TcConvParams& p) {
-  const SmemPlan s = smem_plan(p);
-  return s.a_bytes + (size_t)s.nst * s.w_stage_bytes;
-}
+// bytes of dynamic shared memory of the launch
+size_t tc_conv_smem_bytes(const TcConvParams& p) { return smem_plan(p).total; }
 
 cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream) {
   {  // per-device attribute; cheap enough to set on every launch
@@ -276,10 +294,9 @@ cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream
     if (e != cudaSuccess) return e;
   }
   const SmemPlan sp = smem_plan(p);
-  const size_t smem = sp.a_bytes + (size_t)sp.nst * sp.w_stage_bytes;
-  if (smem > SMEM_MAX) return cudaErrorInvalidConfiguration;
+  if (sp.total > SMEM_MAX) return cudaErrorInvalidConfiguration;
   const dim3 grid(ceil_div(p.Lt, TC_TILE_M), p.ngroups, batch);
-  tc_conv_kernel<<<grid, NT, smem, stream>>>(p, sp.w_stage_bytes, sp.nst);
+  tc_conv_kernel<<<grid, NT, sp.total, stream>>>(p, sp.kb_stage, sp.nst);
   return cudaGetLastError();
 }
 

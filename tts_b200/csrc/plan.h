@@ -20,7 +20,7 @@ struct ConvF32 {
 struct TcGroupPlan {
   size_t w_off = 0;     // bf16-element offset into the plan's bf16 blob
   size_t bias_off = 0;  // float offset into the fp32 blob, [ncols]
-  int ncols = 0, tap_shift = 0, phase_first = 0, ch_first = 0;
+  int ncols = 0, col_first = 0;
 };
 struct TcLayer {
   int cin_pad = 0, cout_pad = 0, cout = 0, up_f = 1;

@@ -16,57 +16,54 @@ struct Bf16Builder {
   }
 };
 
-struct PhaseClass {
-  int phase_first, n_phases, tap_shift;
-};
-
 inline int pad16(int c) { return (int)round_up(c, 16); }
 
+// Packs one layer for the tcgen05 conv kernel.  Layer columns are ordered [plane][phase][8 channels]
+// (tc_conv.cuh), split into groups of <= 256 columns that hold whole planes.
 // wfun(src, tap, ci, phase, co) / bfun(co): reference weights; channels beyond the real counts are zero.
 template <class WF, class BF>
 int pack_tc_layer(Bf16Builder& b16, BlobBuilder& bb, TcLayer& L, int nsrc, const int* taps, const int* cin, int cout,
-                  int up_f, const std::vector<PhaseClass>& classes, WF wfun, BF bfun) {
+                  int up_f, WF wfun, BF bfun) {
   L.cin_pad = pad16(cin[0]);
   L.cout_pad = pad16(cout);
   L.cout = cout;
   L.up_f = up_f;
   L.groups.clear();
-  for (const PhaseClass& pc : classes) {
-    const int flat = pc.n_phases * L.cout_pad;
-    int ncols = 16;
-    for (int n = 256; n >= 16; n -= 16)
-      if (flat % n == 0) { ncols = n; break; }
-    for (int col0 = 0; col0 < flat; col0 += ncols) {
-      TcGroupPlan g;
-      g.ncols = ncols;
-      g.tap_shift = pc.tap_shift;
-      g.phase_first = pc.phase_first + col0 / L.cout_pad;
-      g.ch_first = col0 % L.cout_pad;
-      size_t total = 0;
-      for (int s = 0; s < nsrc; ++s) total += (size_t)taps[s] * pad16(cin[s]) * ncols;
-      g.w_off = b16.alloc(total);
-      g.bias_off = bb.alloc(ncols);
-      size_t base = g.w_off;
-      for (int s = 0; s < nsrc; ++s) {
-        const int cp = pad16(cin[s]);
-        for (int j = 0; j < taps[s]; ++j) {
-          for (int ci = 0; ci < cin[s]; ++ci)
-            for (int col = 0; col < ncols; ++col) {
-              const int fl = g.ch_first + col;
-              const int ph = g.phase_first + fl / L.cout_pad, co = fl % L.cout_pad;
-              if (co >= cout) continue;
-              b16.data[base + ((size_t)(ci >> 3) * ncols + col) * 8 + (ci & 7)] =
-                  __float2bfloat16(wfun(s, j, ci, ph, co));
-            }
-          base += (size_t)cp * ncols;
-        }
+  const int total = up_f * L.cout_pad;
+  int unit = 8 * up_f;                       // one plane
+  while (unit % 16) unit *= 2;
+  if (unit > 256) return fail(TTSB200_ERR_INVALID, "upsample factor too large for the BF16 path");
+  int ncols = unit;
+  for (int n = 256 / unit * unit; n >= unit; n -= unit)
+    if (total % n == 0) { ncols = n; break; }
+  for (int col0 = 0; col0 < total; col0 += ncols) {
+    TcGroupPlan g;
+    g.ncols = ncols;
+    g.col_first = col0;
+    size_t tot = 0;
+    for (int s = 0; s < nsrc; ++s) tot += (size_t)taps[s] * pad16(cin[s]) * ncols;
+    g.w_off = b16.alloc(tot);
+    g.bias_off = bb.alloc(ncols);
+    size_t base = g.w_off;
+    for (int s = 0; s < nsrc; ++s) {
+      const int cp = pad16(cin[s]);
+      for (int j = 0; j < taps[s]; ++j) {
+        for (int ci = 0; ci < cin[s]; ++ci)
+          for (int col = 0; col < ncols; ++col) {
+            const int fl = col0 + col;
+            const int plane = fl / (8 * up_f), ph = (fl / 8) % up_f, co = plane * 8 + fl % 8;
+            if (co >= cout) continue;
+            b16.data[base + ((size_t)(ci >> 3) * ncols + col) * 8 + (ci & 7)] = __float2bfloat16(wfun(s, j, ci, ph, co));
+          }
+        base += (size_t)cp * ncols;
       }
-      for (int col = 0; col < ncols; ++col) {
-        const int co = (g.ch_first + col) % L.cout_pad;
-        bb.data[g.bias_off + col] = co < cout ? bfun(co) : 0.f;
-      }
-      L.groups.push_back(g);
     }
+    for (int col = 0; col < ncols; ++col) {
+      const int fl = col0 + col;
+      const int co = fl / (8 * up_f) * 8 + fl % 8;
+      bb.data[g.bias_off + col] = co < cout ? bfun(co) : 0.f;
+    }
+    L.groups.push_back(g);
   }
   if ((int)L.groups.size() > TC_MAX_GROUPS) return fail(TTSB200_ERR_INVALID, "layer needs too many column groups");
   return 0;
@@ -75,14 +72,13 @@ int pack_tc_layer(Bf16Builder& b16, BlobBuilder& bb, TcLayer& L, int nsrc, const
 // tensors[] in ttsb200_plan_create order; fills plan->tc_* and uploads plan->blob16 later.
 int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, Bf16Builder& b16) {
   const ttsb200_generator_config& cfg = plan->cfg;
-  const std::vector<PhaseClass> plain{{0, 1, 0}};
   int ti = 0;
   int max_d = (cfg.proj_kernel - 1) / 2;
   {
     const float *w = tensors[ti], *b = tensors[ti + 1];
     const int taps[1] = {cfg.proj_kernel}, cin[1] = {cfg.in_channels};
     const int Cin = cfg.in_channels, k = cfg.proj_kernel;
-    if (int rc = pack_tc_layer(b16, bb, plan->tc_proj, 1, taps, cin, cfg.base_channels, 1, plain,
+    if (int rc = pack_tc_layer(b16, bb, plan->tc_proj, 1, taps, cin, cfg.base_channels, 1,
                                [&](int, int j, int ci, int, int co) { return w[((size_t)co * Cin + ci) * k + j]; },
                                [&](int co) { return b[co]; }))
       return rc;
@@ -94,15 +90,12 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
     {
       const float *w = tensors[ti], *b = tensors[ti + 1];
       const int f = sp.f, P = sp.P, Cout = sp.Cout;
-      // phases with (r + P) / f == 0 read x[m], x[m-1]; the rest read x[m+1], x[m]
-      const int n0 = std::max(0, std::min(f, f - P));
-      std::vector<PhaseClass> classes;
-      if (n0 > 0) classes.push_back({0, n0, 0});
-      if (n0 < f) classes.push_back({n0, f - n0, 1});
+      // y[q f - P + r] = x[q] w[r] + x[q-1] w[r + f]   (GEMM row q = 0..Lin, phase r = 0..f-1)
       const int taps[1] = {2}, cin[1] = {sp.Cin};
-      if (int rc = pack_tc_layer(b16, bb, sp.tc_up, 1, taps, cin, Cout, f, classes,
+      (void)P;
+      if (int rc = pack_tc_layer(b16, bb, sp.tc_up, 1, taps, cin, Cout, f,
                                  [&](int, int j, int ci, int ph, int co) {
-                                   return w[((size_t)ci * Cout + co) * (2 * f) + (ph + P) % f + f * j];
+                                   return w[((size_t)ci * Cout + co) * (2 * f) + ph + f * j];
                                  },
                                  [&](int co) { return b[co]; }))
         return rc;
@@ -118,14 +111,14 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
       const float *ws = tensors[ti_short + 2 * bi], *bs = tensors[ti_short + 2 * bi + 1];
       {
         const int taps[1] = {k}, cin[1] = {C};
-        if (int rc = pack_tc_layer(b16, bb, bp.tc_conv1, 1, taps, cin, C, 1, plain,
+        if (int rc = pack_tc_layer(b16, bb, bp.tc_conv1, 1, taps, cin, C, 1,
                                    [&](int, int j, int ci, int, int co) { return w1[((size_t)co * C + ci) * k + j]; },
                                    [&](int co) { return b1[co]; }))
           return rc;
       }
       {
         const int taps[2] = {1, 1}, cin[2] = {C, C};
-        if (int rc = pack_tc_layer(b16, bb, bp.tc_conv2s, 2, taps, cin, C, 1, plain,
+        if (int rc = pack_tc_layer(b16, bb, bp.tc_conv2s, 2, taps, cin, C, 1,
                                    [&](int src, int, int ci, int, int co) {
                                      return (src == 0 ? w2 : ws)[(size_t)co * C + ci];
                                    },
@@ -140,7 +133,7 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
     const float *w = tensors[ti], *b = tensors[ti + 1];
     const int taps[1] = {cfg.proj_kernel}, cin[1] = {clast};
     const int k = cfg.proj_kernel;
-    if (int rc = pack_tc_layer(b16, bb, plan->tc_head, 1, taps, cin, cfg.out_channels, 1, plain,
+    if (int rc = pack_tc_layer(b16, bb, plan->tc_head, 1, taps, cin, cfg.out_channels, 1,
                                [&](int, int j, int ci, int, int co) { return w[((size_t)co * clast + ci) * k + j]; },
                                [&](int co) { return b[co]; }))
       return rc;
@@ -222,18 +215,17 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     p.ngroups = (int)L.groups.size();
     for (int g = 0; g < p.ngroups; ++g) {
       const TcGroupPlan& gp = L.groups[g];
-      p.grp[g] = TcGroup{Wh + gp.w_off, Wf + gp.bias_off, gp.ncols, gp.tap_shift, gp.phase_first, gp.ch_first};
+      p.grp[g] = TcGroup{Wh + gp.w_off, Wf + gp.bias_off, gp.ncols, gp.col_first};
     }
-    p.Lt = (int)Lt; p.up_f = L.up_f; p.cout_pad = L.cout_pad; p.cout_real = L.cout; p.slope = slope;
+    p.Lt = (int)Lt; p.up_f = L.up_f; p.up_P = 0; p.cout_real = L.cout; p.slope = slope;
     return p;
   };
-  auto src = [&](const __nv_bfloat16* x, int C, int64_t L, int taps, int step, int first, bool lrelu,
-                 int extra_hi = 0) {
+  auto src = [&](const __nv_bfloat16* x, int C, int64_t L, int taps, int step, int first, bool lrelu) {
     const CanonDims d = canon_dims(plan, C, L);
     TcSrc s{};
     s.x = x; s.batch_stride = (int64_t)d.elems; s.planes = d.planes; s.plane_rows = d.rows;
     const int lo = std::min(first, first + (taps - 1) * step);
-    const int hi = std::max(first, first + (taps - 1) * step) + extra_hi;   // extra_hi: room for the group shift
+    const int hi = std::max(first, first + (taps - 1) * step);
     s.row_base = halo + lo; s.rows = TC_TILE_M + (hi - lo); s.taps = taps;
     for (int j = 0; j < taps; ++j) s.tap_row[j] = first + j * step - lo;
     s.lrelu = lrelu ? 1 : 0;
@@ -245,7 +237,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     p.out_halo = halo; p.out_L = (int)L; p.out_lrelu = lrelu ? 1 : 0; p.margin = margin;
   };
   auto run = [&](const char* name, int layer, const TcConvParams& p, double macs, double io_elems) -> int {
-    if (tc_conv_smem_bytes(p) > 227 * 1024 - 1024)
+    if (tc_conv_smem_bytes(p) > 224 * 1024)
       return fail(TTSB200_ERR_INVALID, std::string(name) + ": tile does not fit shared memory on the BF16 path");
     TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, st); }));
     return 0;
@@ -283,8 +275,9 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     const int C = sp.Cout;
     const bool last_stage = s == S - 1;
     {
-      TcConvParams p = base(sp.tc_up, Lin);
-      p.src[0] = src(cur, sp.Cin, Lin, 2, -1, 0, false, 1);   // taps read x[m + q], x[m + q - 1], q in {0, 1}
+      TcConvParams p = base(sp.tc_up, Lin + 1);               // GEMM rows q = 0..Lin
+      p.up_P = sp.P;
+      p.src[0] = src(cur, sp.Cin, Lin, 2, -1, 0, false);      // taps read x[q], x[q - 1] (zero rows at -1 and Lin)
       // consumer: block 0 (raw x + reflect) or, with no blocks, the next transposed conv / head
       if (nb > 0) canon_out(p, nxt, C, L, false, 1);
       else canon_out(p, nxt, C, L, true, last_stage ? 1 : 2);

@@ -8,9 +8,8 @@
 namespace ttsb {
 
 constexpr int TC_MAX_TAPS = 8;
-constexpr int TC_TILE_M = 128;   // output rows (time positions) per CTA = UMMA M
-constexpr int TC_KB = 64;        // channels per weight pipeline stage
-constexpr int TC_STAGES = 3;
+constexpr int TC_TILE_M = 128;   // GEMM rows (time positions) per CTA = UMMA M
+constexpr int TC_MAX_STAGES = 4; // weight ring depth
 
 // Activations are "canonical": [batch][C_pad/8 planes][plane_rows][8] bf16, plane row = halo + t.
 struct TcSrc {
@@ -21,18 +20,18 @@ struct TcSrc {
   int row_base;           // global plane row of smem row 0 when t0 == 0  (= halo + min tap shift)
   int rows;               // rows staged in shared memory (TC_TILE_M + tap span)
   int taps;
-  int tap_row[TC_MAX_TAPS];  // smem row of output row 0 for tap j (before the group's shift)
+  int tap_row[TC_MAX_TAPS];  // smem row of GEMM row 0 for tap j
   int lrelu;              // LeakyReLU applied in shared memory before the MMAs read it
 };
 
-// One CTA column-group: <= 256 accumulator columns of the flattened [phase][C_out_pad] axis.
+// One CTA column group: <= 256 accumulator columns.  The layer's columns are ordered [plane][phase][8]:
+// 8 output channels x all `up_f` phases of a transposed conv are adjacent, so one thread's values for a
+// plane form `up_f` consecutive 16-byte rows of the output tensor.
 struct TcGroup {
   const __nv_bfloat16* w;  // [src][tap][C_pad/8][ncols][8]
   const float* bias;       // [ncols]
-  int ncols;               // multiple of 16
-  int tap_shift;           // added to every tap row (transposed conv: q = (r+P)/f)
-  int phase_first;         // upsample phase of column 0
-  int ch_first;            // channel (within the phase) of column 0
+  int ncols;               // multiple of 16 and of 8 * up_f
+  int col_first;           // first layer column of the group
 };
 
 constexpr int TC_MAX_GROUPS = 16;
@@ -42,9 +41,8 @@ struct TcConvParams {
   int nsrc;
   TcGroup grp[TC_MAX_GROUPS];
   int ngroups;
-  int Lt;                 // GEMM rows (input positions for transposed conv, else output positions)
-  int up_f;               // output row = m * up_f + phase
-  int cout_pad;           // columns per phase
+  int Lt;                 // GEMM rows: output positions, or input positions + 1 for a transposed conv
+  int up_f, up_P;         // output row of GEMM row q, phase r:  q * up_f - up_P + r   (plain conv: 1, 0)
   // output
   int out_mode;           // 0: canonical bf16   1: fp32 NCL + tanh
   __nv_bfloat16* out_c;   // canonical out
