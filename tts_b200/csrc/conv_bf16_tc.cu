@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "tc_conv.cuh"
+#include "trace.cuh"
 
 namespace ttsb {
 
@@ -23,7 +24,8 @@ using namespace tc;
 
 namespace {
 
-constexpr int NT = 192;
+constexpr int NT = 320;            // producer, MMA issuer, 8 epilogue warps (two per TMEM lane quarter)
+constexpr int EPI_THREADS = 256;
 
 __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcConvParams p, const int kb_stage,
                                                       const int nst) {
@@ -51,7 +53,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
 
   if (tid == 0) {
     mbar_init(&bar_a, 1);
-    mbar_init(&bar_a_ready, 128);
+    mbar_init(&bar_a_ready, EPI_THREADS);
     mbar_init(&bar_d, 1);
     for (int s = 0; s < nst; ++s) {
       mbar_init(&bar_full[s], 1);
@@ -68,6 +70,8 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
 
   if (warp == 0) {
     if (elect_one()) {
+      Tracer tr = make_tracer(p.trace, 0, true);
+      tr(10);
       // ---- activation tile(s): one bulk copy per 8-channel plane
       mbar_expect_tx(&bar_a, a_bytes0 + a_bytes1);
       for (int s = 0; s < p.nsrc; ++s) {
@@ -89,6 +93,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
             const int st = it % nst;
             const uint32_t ph = (it / nst) & 1;
             mbar_wait(&bar_empty[st], ph ^ 1);
+            tr(11);
             const uint32_t bytes = (uint32_t)(kb / 8) * ncols * 16;
             mbar_expect_tx(&bar_full[st], bytes);
             bulk_g2s(sW + (size_t)st * w_stage_bytes, gw, bytes, &bar_full[st]);
@@ -99,13 +104,16 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
   } else if (warp == 1) {
     // ---- MMA issuer: the whole warp walks the loops (addresses stay in uniform registers), one lane issues
     const bool leader = elect_one() != 0;
-    if (need_lrelu) mbar_wait(&bar_a_ready, 0); else mbar_wait(&bar_a, 0);
+    Tracer tr = make_tracer(p.trace, 1, leader);
+    tr(20);
+    mbar_wait(&bar_a, 0);          // activation tile(s) landed
+    mbar_wait(&bar_a_ready, 0);    // ... LeakyReLU'd in place if asked, and the accumulator holds the bias
     tc_fence_after();
+    tr(21);
     const uint32_t idesc = make_idesc_bf16(TC_TILE_M, ncols);
     const uint32_t lbo_b = (uint32_t)ncols * 16;
     const uint64_t b_tmpl = make_desc(0, lbo_b, 128);
     int it = 0;
-    uint32_t acc = 0;
     for (int s = 0; s < p.nsrc; ++s) {
       const TcSrc& S = p.src[s];
       const int cp = S.planes * 8;
@@ -120,27 +128,47 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
           const uint32_t ph = (it / nst) & 1;
           mbar_wait(&bar_full[st], ph);
           tc_fence_after();
+          tr(22);
           if (leader) {
             uint32_t a_lo = (a_tap + (uint32_t)(c0 >> 3) * lbo_a) >> 4;
             uint32_t b_lo = smem_u32(sW + (size_t)st * w_stage_bytes) >> 4;
             for (int kk = 0; kk < kb / 16; ++kk) {
-              umma_bf16(tbase, a_tmpl | a_lo, b_tmpl | b_lo, idesc, acc);
-              acc = 1;
+              umma_bf16(tbase, a_tmpl | a_lo, b_tmpl | b_lo, idesc, 1);
               a_lo += lbo_a >> 3;   // two planes further, in 16-byte units
               b_lo += lbo_b >> 3;
             }
             umma_commit(&bar_empty[st]);  // frees the stage once these MMAs have read it
           }
-          acc = 1;
           __syncwarp();
         }
       }
     }
     if (leader) umma_commit(&bar_d);
     __syncwarp();
+    tr(23);
   } else {
-    // ---- warps 2..5: optional LeakyReLU over the staged tile, then the epilogue
+    // ---- warps 2..9: bias -> accumulator, optional LeakyReLU over the staged tile, then the epilogue.
+    // Two warps share a TMEM lane quarter and take alternate 32-column batches.
     const int et = tid - 64;
+    const int q4 = warp & 3;                 // TMEM lane quarter this warp may touch
+    const int hf = (warp - 2) >> 2;          // which of the alternating batches
+    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
+    Tracer tr = make_tracer(p.trace, 2, et == 0);
+    tr(30);
+    // the accumulator starts from the bias row, so the MMAs always accumulate and the epilogue has no add
+    for (int c = hf * 32; c < ncols; c += 64) {
+      const int nc = min(32, ncols - c);
+      uint32_t bv[32];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 f4 = *reinterpret_cast<const float4*>(&s_bias[min(c + 4 * i, ncols - 4)]);
+        bv[4 * i] = __float_as_uint(f4.x); bv[4 * i + 1] = __float_as_uint(f4.y);
+        bv[4 * i + 2] = __float_as_uint(f4.z); bv[4 * i + 3] = __float_as_uint(f4.w);
+      }
+      tmem_st<16>(trow + c, bv);
+      if (nc > 16) tmem_st<16>(trow + c + 16, bv + 16);
+    }
+    tmem_wait_st();
     if (need_lrelu) {
       const Slope2 slope2 = make_slope2(p.slope);
       mbar_wait(&bar_a, 0);
@@ -148,7 +176,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
         if (!p.src[s].lrelu) continue;
         uint4* v = reinterpret_cast<uint4*>(s ? sA1 : sA0);
         const int nvec = (s ? a_bytes1 : a_bytes0) / 16;
-        for (int e = et; e < nvec; e += 128) {
+        for (int e = et; e < nvec; e += EPI_THREADS) {
           uint4 u = v[e];
           u.x = lrelu_bf16x2(u.x, slope2); u.y = lrelu_bf16x2(u.y, slope2);
           u.z = lrelu_bf16x2(u.z, slope2); u.w = lrelu_bf16x2(u.w, slope2);
@@ -156,65 +184,83 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
         }
       }
       fence_proxy_async();
-      mbar_arrive(&bar_a_ready);
     }
+    tc_fence_before();
+    mbar_arrive(&bar_a_ready);
+    tr(31);
     mbar_wait_relaxed(&bar_d, 0);
     tc_fence_after();
-    const int q4 = warp & 3;                 // TMEM lane quarter this warp may read
+    tr(32);
     const int q = t0 + q4 * 32 + lane;       // GEMM row of this thread
     const bool row_ok = q < p.Lt;
-    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
     const int f = p.up_f;
     const int row0 = q * f - p.up_P;         // output row of phase 0
     __nv_bfloat16* ob = p.out_c + (int64_t)b * p.out_batch_stride;
-    for (int c = 0; c < ncols; c += 32) {
+    // (plane, phase) of the first 8-column unit; advanced incrementally (no division in the loop)
+    int plane = ((G.col_first >> 3) + hf * 4) / f, r = ((G.col_first >> 3) + hf * 4) - plane * f;
+    const int out_L = p.out_L, halo = p.out_halo, margin = p.margin;
+    const bool to_canon = p.out_mode == 0, act = p.out_lrelu != 0;
+    const float slope = p.slope;
+    // rows that also own halo rows of the output (mirror / zero margins) are rare: test once per thread
+    const bool near_edge = row0 <= halo || row0 + f - 1 >= out_L - 1 - halo;
+    for (int c = hf * 32; c < ncols; c += 64) {
       const int nc = min(32, ncols - c);     // 16 or 32
       uint32_t v[32];
       tmem_ld16_nw(trow + c, v);
       if (nc > 16) tmem_ld16_nw(trow + c + 16, v + 16);
       tmem_wait_ld();
-      if (!row_ok) continue;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {          // 8-column units: one (plane, phase) each
-        if (u * 8 >= nc) break;
-        const int unit = ((G.col_first + c) >> 3) + u;
-        const int plane = unit / f, r = unit - plane * f;
-        const int tau = row0 + r;
-        if (tau < 0 || tau >= p.out_L) continue;
-        const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[c + u * 8]);
-        const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[c + u * 8 + 4]);
-        float y[8];
-        y[0] = __uint_as_float(v[u * 8 + 0]) + b0.x; y[1] = __uint_as_float(v[u * 8 + 1]) + b0.y;
-        y[2] = __uint_as_float(v[u * 8 + 2]) + b0.z; y[3] = __uint_as_float(v[u * 8 + 3]) + b0.w;
-        y[4] = __uint_as_float(v[u * 8 + 4]) + b1.x; y[5] = __uint_as_float(v[u * 8 + 5]) + b1.y;
-        y[6] = __uint_as_float(v[u * 8 + 6]) + b1.z; y[7] = __uint_as_float(v[u * 8 + 7]) + b1.w;
-        if (p.out_mode == 0) {
-          if (p.out_lrelu) {
+        if (u * 8 < nc) {
+          const int tau = row0 + r;
+          if (row_ok && tau >= 0 && tau < out_L) {
+            float y[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) y[i] = lrelu_f(y[i], p.slope);
-          }
-          const uint4 w4 = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
-                                      pack_bf16x2(y[6], y[7]));
-          __nv_bfloat16* pb = ob + (int64_t)plane * p.out_plane_rows * 8;
-          *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo + tau) * 8) = w4;
-          if (p.margin == 1) {           // halo rows mirror the interior (ReflectionPad1d of the consumer)
-            if (tau >= 1 && tau <= p.out_halo) *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo - tau) * 8) = w4;
-            const int back = p.out_L - 1 - tau;
-            if (back >= 1 && back <= p.out_halo)
-              *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo + p.out_L - 1 + back) * 8) = w4;
-          } else if (p.margin == 2) {    // zero rows either side (transposed conv of the consumer)
-            const uint4 z = make_uint4(0, 0, 0, 0);
-            if (tau == 0) *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo - 1) * 8) = z;
-            if (tau == p.out_L - 1) *reinterpret_cast<uint4*>(pb + (int64_t)(p.out_halo + p.out_L) * 8) = z;
-          }
-        } else {
-          float* of = p.out_f + ((int64_t)b * p.cout_real + plane * 8) * p.out_L + tau;
+            for (int i = 0; i < 8; ++i) y[i] = __uint_as_float(v[u * 8 + i]);
+            if (to_canon) {
+              if (act) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            if (plane * 8 + i < p.cout_real) of[(int64_t)i * p.out_L] = tanhf(y[i]);
+                for (int i = 0; i < 8; ++i) y[i] = lrelu_f(y[i], slope);
+              }
+              const uint4 w4 = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
+                                          pack_bf16x2(y[6], y[7]));
+              __nv_bfloat16* pb = ob + (int64_t)plane * p.out_plane_rows * 8;
+              *reinterpret_cast<uint4*>(pb + (int64_t)(halo + tau) * 8) = w4;
+              if (near_edge) {
+                if (margin == 1) {         // halo rows mirror the interior (ReflectionPad1d of the consumer)
+                  if (tau >= 1 && tau <= halo) *reinterpret_cast<uint4*>(pb + (int64_t)(halo - tau) * 8) = w4;
+                  const int back = out_L - 1 - tau;
+                  if (back >= 1 && back <= halo) *reinterpret_cast<uint4*>(pb + (int64_t)(halo + out_L - 1 + back) * 8) = w4;
+                } else if (margin == 2) {  // zero rows either side (transposed conv of the consumer)
+                  const uint4 z = make_uint4(0, 0, 0, 0);
+                  if (tau == 0) *reinterpret_cast<uint4*>(pb + (int64_t)(halo - 1) * 8) = z;
+                  if (tau == out_L - 1) *reinterpret_cast<uint4*>(pb + (int64_t)(halo + out_L) * 8) = z;
+                }
+              }
+            } else {
+              float* of = p.out_f + ((int64_t)b * p.cout_real + plane * 8) * out_L + tau;
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                if (plane * 8 + i < p.cout_real) of[(int64_t)i * out_L] = tanhf(y[i]);
+            }
+          }
+          if (++r == f) {
+            r = 0;
+            ++plane;
+          }
         }
       }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)              // skip the partner warp's batch
+        if (++r == f) {
+          r = 0;
+          ++plane;
+        }
     }
+  }
+  if (warp >= 2) {
+    Tracer tr = make_tracer(p.trace, 3, tid == 64);
+    tr(33);
   }
   tc_fence_before();
   __syncthreads();
@@ -288,7 +334,8 @@ SmemPlan smem_plan(const TcConvParams& p) {
 // bytes of dynamic shared memory of the launch
 size_t tc_conv_smem_bytes(const TcConvParams& p) { return smem_plan(p).total; }
 
-cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream) {
+cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, cudaStream_t stream) {
+  TcConvParams p = p_in;
   {  // per-device attribute; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
     if (e != cudaSuccess) return e;
@@ -296,8 +343,11 @@ cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream
   const SmemPlan sp = smem_plan(p);
   if (sp.total > SMEM_MAX) return cudaErrorInvalidConfiguration;
   const dim3 grid(ceil_div(p.Lt, TC_TILE_M), p.ngroups, batch);
+  p.trace = trace_begin(stream);
   tc_conv_kernel<<<grid, NT, sp.total, stream>>>(p, sp.kb_stage, sp.nst);
-  return cudaGetLastError();
+  const cudaError_t rc = cudaGetLastError();
+  trace_end(p.trace, 1000 + p.trace_id, stream);
+  return rc;
 }
 
 cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out, int planes,

@@ -236,7 +236,9 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     p.out_mode = 0; p.out_c = out; p.out_batch_stride = (int64_t)d.elems; p.out_plane_rows = d.rows;
     p.out_halo = halo; p.out_L = (int)L; p.out_lrelu = lrelu ? 1 : 0; p.margin = margin;
   };
-  auto run = [&](const char* name, int layer, const TcConvParams& p, double macs, double io_elems) -> int {
+  int trace_seq = 0;
+  auto run = [&](const char* name, int layer, TcConvParams p, double macs, double io_elems) -> int {
+    p.trace_id = layer * 10 + trace_seq++ % 10;   // label for the debug timeline (trace.cuh)
     if (tc_conv_smem_bytes(p) > 224 * 1024)
       return fail(TTSB200_ERR_INVALID, std::string(name) + ": tile does not fit shared memory on the BF16 path");
     TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, st); }));

@@ -35,6 +35,7 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "tc_conv.cuh"
+#include "trace.cuh"
 
 namespace ttsb {
 
@@ -46,30 +47,10 @@ constexpr int TAPS = 3;
 constexpr int MAX_KT = TC_STACK_MAX_KT;
 
 
-// Timeline capture for CTA 0 (debug aid, enabled by TTSB200_STACK_TRACE=<file>): role r appends {tag, clock64}.
 #ifdef TTSB_STACK_TRACE
 #define DBG(bit) (p.debug & (bit))
-struct Tracer {
-  long long* buf;
-  int n;
-  __device__ __forceinline__ void operator()(int tag) {
-    if (buf && n < 254) {
-      buf[n] = tag;
-      buf[n + 1] = clock64();
-      n += 2;
-    }
-  }
-};
-__device__ __forceinline__ Tracer make_tracer(const TcStackParams& p, int role, bool leader) {
-  return Tracer{(p.trace && blockIdx.x == 0 && leader) ? p.trace + role * 256 : nullptr, 0};
-}
 #else
 #define DBG(bit) false
-// compiled out: the trace points cost instruction-cache space in a kernel that is sensitive to it
-struct Tracer {
-  __device__ __forceinline__ void operator()(int) {}
-};
-__device__ __forceinline__ Tracer make_tracer(const TcStackParams&, int, bool) { return Tracer{}; }
 #endif
 
 struct Bars {
@@ -184,7 +165,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
       const uint32_t lbo_a = plane_bytes;
       // descriptor templates: only the 14-bit start-address field changes between MMAs
       const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
-      Tracer tr = make_tracer(p, 0, leader);
+      Tracer tr = make_tracer(p.trace, 0, leader);
       int gb = 0;
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
         const int buf = it & 1;
@@ -263,7 +244,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
     const Slope2 slope2 = make_slope2(slope);
     const int L = p.L;
     const int pair_bar = 1 + t * 4 + q4;        // named barrier shared by the CS warps of a quarter
-    Tracer tr = make_tracer(p, 1 + t, m == 0 && cs == 0);
+    Tracer tr = make_tracer(p.trace, 1 + t, m == 0 && cs == 0);
 
     int gb = 0;
     for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
@@ -495,25 +476,10 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int items = p.n_chains * batch;
   const int grid = items < sms ? items : sms;
-  const char* trace_path = getenv("TTSB200_STACK_TRACE");
   if (const char* dbg = getenv("TTSB200_STACK_DEBUG")) p.debug = atoi(dbg);
-  if (trace_path) {
-    cudaMalloc(&p.trace, 8 * 256 * sizeof(long long));
-    cudaMemsetAsync(p.trace, 0, 8 * 256 * sizeof(long long), stream);
-  }
-  cudaError_t rc = dispatch(p, smem, grid, stream);
-  if (trace_path && rc == cudaSuccess) {
-    std::vector<long long> h(8 * 256);
-    cudaStreamSynchronize(stream);
-    cudaMemcpy(h.data(), p.trace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
-    cudaFree(p.trace);
-    if (FILE* f = fopen(trace_path, "a")) {
-      for (int r = 0; r < 8; ++r)
-        for (int i = 0; i < 256 && h[r * 256 + i]; i += 2)
-          fprintf(f, "%d %d %d %lld\n", p.cp, r, (int)h[r * 256 + i], h[r * 256 + i + 1]);
-      fclose(f);
-    }
-  }
+  p.trace = trace_begin(stream);
+  const cudaError_t rc = dispatch(p, smem, grid, stream);
+  trace_end(p.trace, p.cp, stream);
   return rc;
 }
 

@@ -55,6 +55,8 @@ struct TcConvParams {
   float* out_f;           // fp32 NCL out [B][cout_real][out_L]
   int cout_real;
   float slope;
+  long long* trace;       // optional timeline buffer (trace.cuh)
+  int trace_id;
 };
 
 // Where a kernel's result goes: canonical bf16 for the next tcgen05 kernel (halo rows filled per the
