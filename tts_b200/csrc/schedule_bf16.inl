@@ -145,8 +145,9 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
   return 0;
 }
 
-// Fused-stack configuration for stage s; kt == 0 when the stage must use the per-conv kernels.
-TcStackParams stack_tiling(const ttsb200_plan* plan, int s) {
+// Fused-stack configuration for stage s; kt == 0 when the stage must use the per-conv kernels.  With
+// `with_head` the output head (LeakyReLU, ReflectionPad1d, Conv1d, Tanh) is folded into the last stage's kernel.
+TcStackParams stack_tiling(const ttsb200_plan* plan, int s, bool with_head = false) {
   const ttsb200_generator_config& cfg = plan->cfg;
   TcStackParams q{};
   q.cp = pad16(plan->stages[s].Cout);
@@ -154,8 +155,23 @@ TcStackParams stack_tiling(const ttsb200_plan* plan, int s) {
   q.res_taps = cfg.res_kernel;
   if (q.nblocks < 1 || q.nblocks > TC_STACK_MAX_BLOCKS) return q;
   for (int bi = 0; bi < q.nblocks; ++bi) q.dil[bi] = plan->stages[s].blocks[bi].dilation;
+  if (with_head) {
+    const TcGroupPlan& g = plan->tc_head.groups[0];
+    q.head_w = plan->blob16 + g.w_off;
+    q.head_b = plan->blob + g.bias_off;
+    q.head_taps = cfg.proj_kernel;
+    q.head_ch = cfg.out_channels;
+  }
   if (!tc_stack_configure(q)) q.kt = 0;
   return q;
+}
+// The head rides on the last stage's fused kernel when that kernel exists, the head fits its N = 16 tile and
+// no per-layer taps were asked for (the stack output is then never materialised).
+bool head_fusable(const ttsb200_plan* plan) {
+  const ttsb200_generator_config& cfg = plan->cfg;
+  const int s = cfg.n_stages - 1;
+  return cfg.out_channels <= 16 && plan->tc_head.groups.size() == 1 && plan->tc_head.groups[0].ncols == 16 &&
+         stack_tiling(plan, s, true).kt > 0;
 }
 
 struct CanonDims {
@@ -271,6 +287,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     if (int rc = tap(1, cur, cfg.base_channels, sh.L0, true)) return rc;
   }
   int64_t Lin = sh.L0;
+  bool head_done = false;
   for (int s = 0; s < S; ++s) {
     const StagePlan& sp = plan->stages[s];
     const int64_t L = sh.L[s];
@@ -291,7 +308,8 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       if (int rc = tap(sp.layer_up, cur, C, L, nb == 0)) return rc;
     }
     const int half = (cfg.res_kernel - 1) / 2;
-    TcStackParams q = stack_tiling(plan, s);
+    const bool fuse_head = last_stage && a->n_taps == 0 && head_fusable(plan);
+    TcStackParams q = stack_tiling(plan, s, fuse_head);
     if (q.kt > 0) {  // whole ResidualStack in one kernel
       const CanonDims din = canon_dims(plan, C, L);
       q.x = cur; q.x_batch_stride = (int64_t)din.elems; q.x_plane_rows = din.rows; q.x_halo = halo;
@@ -304,9 +322,16 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         q.b2s[bi] = Wf + bp.tc_conv2s.groups[0].bias_off;
       }
       q.out = TcCanonOut{nxt, (int64_t)din.elems, din.rows, halo, (int)L, 1, last_stage ? 1 : 2};
-      const double macs = (double)(cfg.res_kernel + 2) * nb * C * C * L * B;
-      TTSB_CUDA(ln.run("bf16.resstack.fused", sp.layer_stack, 2 * macs,
-                       2.0 * (2.0 * B * C * L + (double)(cfg.res_kernel + 2) * nb * C * C),
+      double macs = (double)(cfg.res_kernel + 2) * nb * C * C * L * B;
+      double bytes = 2.0 * (2.0 * B * C * L + (double)(cfg.res_kernel + 2) * nb * C * C);
+      if (fuse_head) {
+        const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
+        q.head_out = to_out ? a->out : headf;
+        macs += (double)cfg.proj_kernel * C * cfg.out_channels * L * B;
+        bytes = 2.0 * B * C * L + 4.0 * B * cfg.out_channels * L;
+        head_done = true;
+      }
+      TTSB_CUDA(ln.run(fuse_head ? "bf16.resstack.fused+head" : "bf16.resstack.fused", sp.layer_stack, 2 * macs, bytes,
                        [&] { return tc_stack_launch(q, B, st); }));
       std::swap(cur, nxt);
     } else
@@ -343,13 +368,15 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     const int Cl = plan->stages.back().Cout;
     const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
     float* dst = to_out ? a->out : headf;
-    TcConvParams p = base(plan->tc_head, Lin);
-    p.src[0] = src(cur, Cl, Lin, cfg.proj_kernel, 1, -pp, false);
-    p.out_mode = 1; p.out_f = dst; p.out_L = (int)Lin;
     const int ih = 4 + 3 * S;
-    if (int rc = run("bf16.head.k7+tanh", ih, p, (double)cfg.proj_kernel * Cl * cfg.out_channels * Lin * B,
-                     (double)B * (Cl + 2.0 * cfg.out_channels) * Lin))
-      return rc;
+    if (!head_done) {
+      TcConvParams p = base(plan->tc_head, Lin);
+      p.src[0] = src(cur, Cl, Lin, cfg.proj_kernel, 1, -pp, false);
+      p.out_mode = 1; p.out_f = dst; p.out_L = (int)Lin;
+      if (int rc = run("bf16.head.k7+tanh", ih, p, (double)cfg.proj_kernel * Cl * cfg.out_channels * Lin * B,
+                       (double)B * (Cl + 2.0 * cfg.out_channels) * Lin))
+        return rc;
+    }
     if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
     if (!to_out) {
       const int N = cfg.pqmf_bands;

@@ -55,7 +55,7 @@ constexpr int MAX_KT = TC_STACK_MAX_KT;
 
 struct Bars {
   uint64_t x_full[2], x_free[2];
-  uint64_t w1_full[TC_STACK_MAX_BLOCKS], w2_full[TC_STACK_MAX_BLOCKS], w1_free, w2_free;
+  uint64_t w1_full[TC_STACK_MAX_BLOCKS], w2_full[TC_STACK_MAX_BLOCKS], w1_free, w2_free, wh_full;
   uint64_t xa_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
 };
 
@@ -75,10 +75,14 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
   __shared__ __align__(8) Bars bars;
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float s_bias[TC_STACK_MAX_BLOCKS][2][CP];
+  __shared__ __align__(16) float s_bias_head[16];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = p.guard, RS = TR + 2 * G;
-  const int V = TR - 2 * p.sum_d;
+  const bool head = CS == 1 && p.head_w != nullptr;
+  const int hh = head ? (p.head_taps - 1) / 2 : 0;      // halo of the fused head conv
+  const int V = TR - 2 * (p.sum_d + hh);
+  const int SD = p.sum_d + hh;                          // rows recomputed per chain side
   const int nb = p.nblocks;
   const uint32_t plane_bytes = (uint32_t)RS * 16;
   const uint32_t xa_bytes = (uint32_t)PL * plane_bytes;
@@ -86,6 +90,8 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
   const int wsets = p.w_sets;  // nb: every block's weights stay resident; 1: reloaded per block
   uint8_t* sXA = smem;
   uint8_t* sW = smem + 2 * xa_bytes;   // [set][W1 | W2S]
+  uint8_t* sWH = sW + (size_t)wsets * (W1_BYTES + W2_BYTES);   // head weights [taps][CP/8][16][8]
+  const uint32_t wh_bytes = head ? (uint32_t)p.head_taps * CP * 16 * 2 : 0;
 
   const int n_items = p.n_chains * p.batch;
 
@@ -100,6 +106,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
     }
     mbar_init(&bars.w1_free, 1);
     mbar_init(&bars.w2_free, 1);
+    mbar_init(&bars.wh_full, 1);
     for (int t = 0; t < KT; ++t) {
       mbar_init(&bars.xa_ready[t], GROUP_THREADS);
       mbar_init(&bars.d1_full[t], 1);
@@ -114,6 +121,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
     const int blk = e / (2 * CP), r = e - blk * 2 * CP;
     s_bias[blk][r / CP][r % CP] = r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP];
   }
+  if (head && tid < 16) s_bias_head[tid] = p.head_b[tid];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -128,7 +136,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
         const int buf = it & 1;
         if (it >= 2) mbar_wait(&bars.x_free[buf], ((it >> 1) - 1) & 1);
         const int b = item / p.n_chains, chain = item - b * p.n_chains;
-        const int g0 = chain * V - p.sum_d;
+        const int g0 = chain * V - SD;
         mbar_expect_tx(&bars.x_full[buf], (uint32_t)PL * TR * 16);
         const __nv_bfloat16* gx = p.x + (int64_t)b * p.x_batch_stride + (int64_t)(p.x_halo + g0) * 8;
         uint8_t* dst = sXA + (size_t)buf * xa_bytes + (size_t)G * 16;
@@ -137,6 +145,10 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
                    &bars.x_full[buf]);
       };
       load_x(0);
+      if (head) {
+        mbar_expect_tx(&bars.wh_full, wh_bytes);
+        bulk_g2s(sWH, p.head_w, wh_bytes, &bars.wh_full);
+      }
       int gb = 0;
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
         for (int blk = 0; blk < nb; ++blk, ++gb) {
@@ -167,6 +179,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
       const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
       Tracer tr = make_tracer(p.trace, 0, leader);
       int gb = 0;
+      uint32_t n_xa = 0;   // completed xa_ready rounds (one per block, plus one per item with a fused head)
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
         const int buf = it & 1;
         const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
@@ -180,8 +193,8 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
           else if (it == 0) mbar_wait(&bars.w1_full[set], 0);
 #pragma unroll 1
           for (int t = 0; t < KT; ++t) {
-            if (t == 0) mbar_wait(&bars.xa_ready[0], ph);
-            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], ph);
+            if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
+            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
             tc_fence_after();
             tr(100 + t);
             const uint32_t dcol = tbase + t * TCOLS;
@@ -200,9 +213,10 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
             __syncwarp();
             tr(110 + t);
           }
+          ++n_xa;
           if (leader) {
             if (wsets == 1) umma_commit(&bars.w1_free);
-            if (blk == nb - 1) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
+            if (blk == nb - 1 && !head) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
           }
           __syncwarp();
           // ---- 1x1 conv on h (TMEM) + 1x1 shortcut on raw x (TMEM): D2[t]
@@ -230,6 +244,34 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
           if (leader && wsets == 1) umma_commit(&bars.w2_free);
           __syncwarp();
         }
+        if (head) {
+          // ---- fused output head: D1[t][0:16] = sum_tap lrelu(x_out)[rows + tap - hh] Wh[tap]^T   (N = 16)
+          constexpr uint32_t idesc_h = make_idesc_bf16(128, 16);
+          const uint64_t bh_tmpl = make_desc(0, 16 * 16, 128);
+          const uint32_t wh = smem_u32(sWH);
+          if (it == 0) mbar_wait(&bars.wh_full, 0);
+#pragma unroll 1
+          for (int t = 0; t < KT; ++t) {
+            if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
+            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
+            tc_fence_after();
+            if (leader) {
+              for (int j = 0; j < p.head_taps; ++j) {
+                const uint32_t a_row = xa + (uint32_t)(G + t * 128 + j - hh) * 16;
+                const uint32_t w_tap = wh + (uint32_t)j * (CP * 16 * 2);
+#pragma unroll
+                for (int kk = 0; kk < KS; ++kk)
+                  umma_bf16(tbase + t * TCOLS, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
+                            bh_tmpl | (uint64_t)((w_tap + 2 * kk * 256) >> 4), idesc_h, 1);
+              }
+              umma_commit(&bars.d1_full[t]);
+            }
+            __syncwarp();
+          }
+          ++n_xa;
+          if (leader) umma_commit(&bars.x_free[buf]);
+          __syncwarp();
+        }
       }
     }
   } else {
@@ -245,13 +287,14 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
     const int L = p.L;
     const int pair_bar = 1 + t * 4 + q4;        // named barrier shared by the CS warps of a quarter
     Tracer tr = make_tracer(p.trace, 1 + t, m == 0 && cs == 0);
+    uint32_t n_d1 = 0;                          // completed d1_full rounds (blocks, plus the fused head)
 
     int gb = 0;
     for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
       const int item = blockIdx.x + it * gridDim.x;
       const int buf = it & 1;
       const int b = item / p.n_chains, chain = item - b * p.n_chains;
-      const int g0 = chain * V - p.sum_d;       // sequence row of staged row 0
+      const int g0 = chain * V - SD;            // sequence row of staged row 0
       uint8_t* xa = sXA + (size_t)buf * xa_bytes + (size_t)(c0 / 8) * plane_bytes;   // this thread's first plane
 
       // Items whose staged rows stay clear of both sequence ends take the unconditional store path.
@@ -322,7 +365,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
         const bool last = blk == nb - 1;
         // ---- epilogue 1: h = lrelu(D1) -> bf16 over the low columns of D1 (A operand of the 1x1 conv)
         {
-          mbar_wait_relaxed(&bars.d1_full[t], ph);
+          mbar_wait_relaxed(&bars.d1_full[t], n_d1++ & 1);
           tc_fence_after();
           tr(210);
           uint32_t v[CW];
@@ -353,13 +396,20 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
           tmem_wait_ld();
           tr(223);
           uint32_t w[CW / 2];
-          if (!last) {
-            // the 1x1 MMAs of this tile have retired: both accumulators may take the next block's biases
-            init_acc(tlane, s_bias[blk + 1][0]);
-            init_acc(tlane + CP, s_bias[blk + 1][1]);
+          if (!last || head) {
+            if (!last) {
+              // the 1x1 MMAs of this tile have retired: both accumulators may take the next block's biases
+              init_acc(tlane, s_bias[blk + 1][0]);
+              init_acc(tlane + CP, s_bias[blk + 1][1]);
+            } else {
+              uint32_t bv[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_head[i]);
+              tmem_st<16>(tlane, bv);            // head accumulator <- head bias
+            }
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-            if (!DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+            if (!last && !DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
             tr(224);
@@ -407,6 +457,21 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
           }
         }
       }
+      if (head) {
+        // ---- epilogue 3: tanh of the head accumulator -> fp32 [batch][head_ch][L]
+        mbar_wait_relaxed(&bars.d1_full[t], n_d1++ & 1);
+        tc_fence_after();
+        uint32_t v[16];
+        tmem_ld16_nw(tlane, v);
+        tmem_wait_ld();
+        const int tau = g0 + t * 128 + m;
+        if (tau >= chain * V && tau < (chain + 1) * V && tau < L) {
+          float* of = p.head_out + (int64_t)b * p.head_ch * L + tau;
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (i < p.head_ch) of[(int64_t)i * L] = tanhf(__uint_as_float(v[i]));
+        }
+      }
     }
   }
   tc_fence_before();
@@ -449,18 +514,25 @@ bool tc_stack_configure(TcStackParams& p) {
     dmax = dmax > p.dil[i] ? dmax : p.dil[i];
   }
   p.guard = (dmax + 7) / 8 * 8;
-  if (p.kt * 128 - 2 * p.sum_d < 32 || p.guard + p.sum_d > 127) return false;
+  const bool head = p.head_w != nullptr;
+  if (head && (p.cp > 64 || p.head_taps < 1 || p.head_taps > TC_MAX_TAPS || p.head_taps % 2 == 0 || p.head_ch > 16))
+    return false;
+  const int hh = head ? (p.head_taps - 1) / 2 : 0;
+  if (hh > p.guard) p.guard = (hh + 7) / 8 * 8;
+  if (p.kt * 128 - 2 * (p.sum_d + hh) < 32 || p.guard + p.sum_d + hh > 127) return false;
   const size_t xa = 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;
   const size_t wset = (size_t)(TAPS + 2) * p.cp * p.cp * 2;
-  if (xa + wset > SMEM_MAX) return false;
-  p.w_sets = xa + p.nblocks * wset <= SMEM_MAX ? p.nblocks : 1;
+  const size_t wh = head ? (size_t)p.head_taps * p.cp * 16 * 2 : 0;
+  if (xa + wset + wh > SMEM_MAX) return false;
+  p.w_sets = xa + p.nblocks * wset + wh <= SMEM_MAX ? p.nblocks : 1;
   return true;
 }
 
 cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream);
 
 size_t tc_stack_smem_bytes(const TcStackParams& p) {
-  return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2;
+  return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
+         (p.head_w ? (size_t)p.head_taps * p.cp * 16 * 2 : 0);
 }
 
 cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t stream) {
@@ -468,7 +540,7 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
   if (p.kt != tc_stack_kt(p.cp) || p.kt == 0) return cudaErrorInvalidConfiguration;
   const size_t smem = tc_stack_smem_bytes(p);
   if (smem > SMEM_MAX) return cudaErrorInvalidConfiguration;
-  const int V = p.kt * 128 - 2 * p.sum_d;
+  const int V = p.kt * 128 - 2 * (p.sum_d + (p.head_w ? (p.head_taps - 1) / 2 : 0));
   p.batch = batch;
   p.n_chains = ceil_div(p.L, V);
   int dev = 0, sms = 148;

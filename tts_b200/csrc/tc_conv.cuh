@@ -93,6 +93,13 @@ struct TcStackParams {
   int guard;               // spare rows either side of the staged tile (>= max dilation reach)
   int w_sets;              // nblocks: all weights resident in shared memory; 1: streamed per block
   int batch, n_chains;     // filled by tc_stack_launch: work items = batch x n_chains
+  // Optional fused output head (last stage only, cp <= 64): LeakyReLU -> ReflectionPad1d -> Conv1d(k) -> Tanh
+  // (melgan_generator.py:65-77) computed from the stack output while it is still in shared memory; the stack
+  // output itself is then never written to HBM.
+  const __nv_bfloat16* head_w;   // [taps][cp/8][16][8]; nullptr = no head, write the canonical stack output
+  const float* head_b;           // [16]
+  int head_taps, head_ch;        // kernel size (odd, <= TC_MAX_TAPS), real output channels (<= 16)
+  float* head_out;               // fp32 [batch][head_ch][L]
   int debug;               // knock-out bits for timeline experiments (trace builds only)
   long long* trace;        // optional (TTSB200_STACK_TRACE): [role][256] {tag, clock} pairs written by CTA 0
   TcCanonOut out;

@@ -565,6 +565,7 @@ int32_t ttsb200_launch_count(const ttsb200_plan* plan, int32_t precision, int32_
   int launches = 1 + S + 1 + ((plan->cfg.pqmf_bands > 0 && !skip_pqmf) ? 1 : 0);
   for (int s = 0; s < S; ++s)
     launches += (precision == TTSB200_BF16 && n > 0 && stack_tiling(plan, s).kt > 0) ? 1 : 2 * n;
+  if (precision == TTSB200_BF16 && n > 0 && head_fusable(plan)) --launches;   // head folded into the last stack
   return launches + (precision == TTSB200_BF16 ? 1 : 0);
 }
 

@@ -99,7 +99,7 @@ class MelganGenerator(nn.Module):
 
     def _run(self, c, pad, skip_pqmf, tap_layers=None, profile=None):
         eng = self._get_engine()
-        c = c.detach().to(device=eng.device, dtype=torch.float32)
+        c = c.detach().to(device=eng.device, dtype=torch.float32, non_blocking=True)   # async when c is pinned
         prec = _lib.PRECISIONS[self.precision]
         return eng.forward(c, int(pad), prec, skip_pqmf=skip_pqmf, tap_layers=tap_layers, profile=profile)
 
@@ -111,6 +111,20 @@ class MelganGenerator(nn.Module):
 
     def inference(self, c):
         return self._run(c, self.inference_padding, True)
+
+    def inference_to_host(self, c, out=None):
+        """inference() followed by an asynchronous device->host copy into pinned memory, all on the current
+        stream, so the caller's ``.cpu().numpy()`` sync disappears (TTS/server/synthesizer.py:155-159,
+        SURVEY.md §8f-2).  Returns ``(wav_host, event)``: ``wav_host`` (pinned, reusable via ``out=``) is valid
+        once ``event.synchronize()`` returns.  With a pinned ``c`` the upload is asynchronous too, so calls on
+        alternating streams overlap copies with compute."""
+        y = self.inference(c)
+        if out is None:
+            out = torch.empty(y.shape, dtype=y.dtype, pin_memory=True)
+        out.copy_(y, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(y.device))
+        return out, ev
 
     def inference_with_taps(self, c, tap_layers):
         """inference() that also returns {layers[i] index: output} for per-layer parity tests."""
