@@ -263,6 +263,24 @@ def test_bf16_end_to_end_and_per_layer(case, init):
         assert got >= BF16_SNR, got
 
 
+@pytest.mark.parametrize("case", range(len(CASES)))
+def test_bf16_fused_head_matches_unfused(case):
+    """inference() folds the output head into the last stage's kernel; inference_with_taps() runs the stand-alone
+    head kernel on the materialised stack output.  Same arithmetic, so the waveforms agree to bf16 noise on the
+    one tensor (the last stack output) the unfused path rounds once more."""
+    cls, kw, B, T, p = CASES[case]
+    m, spec, sd = default_init(cls, kw)
+    m.inference_padding = p
+    m.precision = "bf16"
+    mel = torch.randn(B, spec.in_channels, T, generator=torch.Generator().manual_seed(17))
+    fused = m.inference(mel).cpu()
+    unfused, _ = m.inference_with_taps(mel, [1])
+    ref = generator_inference(spec, sd, mel, p)
+    assert fused.shape == ref.shape
+    assert snr_db(unfused.cpu(), fused) >= 45.0
+    assert snr_db(ref, fused) >= snr_db(ref, unfused.cpu()) - 1.0
+
+
 def test_bf16_full_size_cfg2_and_golden(golden):
     g = golden("mb_cfg2_item")
     m, spec, sd = default_init("multiband", {})

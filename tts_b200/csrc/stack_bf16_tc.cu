@@ -60,7 +60,8 @@ struct Bars {
 };
 
 template <int CP, int KT, int CS>
-__global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const __grid_constant__ TcStackParams p) {
+__global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ? 2 : 1)
+    tc_stack_kernel(const __grid_constant__ TcStackParams p) {
   constexpr int NT = 64 + KT * CS * 128;
   constexpr int GROUP_THREADS = CS * 128;
   constexpr int PL = CP / 8;          // 8-channel planes
@@ -69,6 +70,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
   constexpr int CW = CP / CS;         // channels per epilogue thread
   constexpr int TCOLS = 5 * CP / 2;   // TMEM columns per tile: D1 | D2 | XR
   static_assert(KT * TCOLS <= 512, "TMEM budget");
+  constexpr uint32_t TMEM_ALLOC = KT * TCOLS <= 128 ? 128 : KT * TCOLS <= 256 ? 256 : 512;   // <= 256: two CTAs share an SM
   static_assert(CW % 8 == 0, "CP must be a multiple of 16");
 
   extern __shared__ __align__(128) uint8_t smem[];
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
     fence_mbar_init();
   }
   constexpr int PRODUCER_WARP = KT * CS * 4, MMA_WARP = PRODUCER_WARP + 1;
-  if (warp == PRODUCER_WARP) tmem_alloc(&tmem_base_s, 512);
+  if (warp == PRODUCER_WARP) tmem_alloc(&tmem_base_s, TMEM_ALLOC);
   for (int e = tid; e < nb * 2 * CP; e += NT) {
     const int blk = e / (2 * CP), r = e - blk * 2 * CP;
     s_bias[blk][r / CP][r % CP] = r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP];
@@ -476,7 +478,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, 1) tc_stack_kernel(const _
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == PRODUCER_WARP) tmem_dealloc(tbase, 512);
+  if (warp == PRODUCER_WARP) tmem_dealloc(tbase, TMEM_ALLOC);
 }
 
 constexpr size_t SMEM_MAX = 227 * 1024 - 6 * 1024;   // static: barriers + bias table (<= 4*2*96*4 B)
@@ -492,12 +494,14 @@ cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t s
 
 }  // namespace
 
+int tc_stack_ctas_per_sm(int cp) { return tc_stack_kt(cp) * 5 * cp / 2 <= 256 ? 2 : 1; }
+
 int tc_stack_kt(int cp) {
   switch (cp) {
     case 96: return 2;
     case 64: return 3;
-    case 48: return 4;
-    case 32: return 4;
+    case 48: return 2;
+    case 32: return 2;
     default: return 0;
   }
 }
@@ -523,8 +527,10 @@ bool tc_stack_configure(TcStackParams& p) {
   const size_t xa = 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;
   const size_t wset = (size_t)(TAPS + 2) * p.cp * p.cp * 2;
   const size_t wh = head ? (size_t)p.head_taps * p.cp * 16 * 2 : 0;
-  if (xa + wset + wh > SMEM_MAX) return false;
-  p.w_sets = xa + p.nblocks * wset + wh <= SMEM_MAX ? p.nblocks : 1;
+  // two CTAs per SM when the TMEM footprint allows it: each then gets half of the shared memory
+  const size_t budget = tc_stack_ctas_per_sm(p.cp) == 2 ? SMEM_MAX / 2 - 1024 : SMEM_MAX;
+  if (xa + wset + wh > budget) return false;
+  p.w_sets = xa + p.nblocks * wset + wh <= budget ? p.nblocks : 1;
   return true;
 }
 
@@ -547,7 +553,8 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int items = p.n_chains * batch;
-  const int grid = items < sms ? items : sms;
+  const int slots = sms * tc_stack_ctas_per_sm(p.cp);
+  const int grid = items < slots ? items : slots;
   if (const char* dbg = getenv("TTSB200_STACK_DEBUG")) p.debug = atoi(dbg);
   p.trace = trace_begin(stream);
   const cudaError_t rc = dispatch(p, smem, grid, stream);
@@ -559,8 +566,8 @@ cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t
   switch (p.cp) {
     case 96: return launch<96, 2, 2>(p, smem, grid, stream);
     case 64: return launch<64, 3, 1>(p, smem, grid, stream);
-    case 48: return launch<48, 4, 1>(p, smem, grid, stream);
-    case 32: return launch<32, 4, 1>(p, smem, grid, stream);
+    case 48: return launch<48, 2, 1>(p, smem, grid, stream);
+    case 32: return launch<32, 2, 1>(p, smem, grid, stream);
     default: return cudaErrorInvalidConfiguration;
   }
 }

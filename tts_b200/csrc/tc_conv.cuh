@@ -105,6 +105,7 @@ struct TcStackParams {
   TcCanonOut out;
   float slope;
 };
+int tc_stack_ctas_per_sm(int cp);                 // 2 when two CTAs' accumulators fit the 512 TMEM columns
 int tc_stack_kt(int cp);                          // 0: this channel count has no fused kernel
 bool tc_stack_configure(TcStackParams& p);        // fills kt / sum_d / guard / w_sets from cp, dil[], nblocks
 size_t tc_stack_smem_bytes(const TcStackParams& p);
