@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
         const bool last = blk == nb - 1;
         // ---- epilogue 1: h = lrelu(D1) -> bf16 over the low columns of D1 (A operand of the 1x1 conv)
         {
-          mbar_wait_relaxed(&bars.d1_full[t], n_d1++ & 1);
+          mbar_wait(&bars.d1_full[t], n_d1++ & 1);
           tc_fence_after();
           tr(210);
           uint32_t v[CW];
@@ -375,9 +375,14 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           tmem_wait_ld();
           tr(212);
           uint32_t w[CW / 2];
+          if (DBG(64)) {
 #pragma unroll
-          for (int i = 0; i < CW / 2; ++i)
-            w[i] = pack_bf16x2(lrelu_f(__uint_as_float(v[2 * i]), slope), lrelu_f(__uint_as_float(v[2 * i + 1]), slope));
+            for (int i = 0; i < CW / 2; ++i) w[i] = v[i];
+          } else {
+#pragma unroll
+            for (int i = 0; i < CW / 2; ++i)
+              w[i] = pack_bf16x2(lrelu_f(__uint_as_float(v[2 * i]), slope), lrelu_f(__uint_as_float(v[2 * i + 1]), slope));
+          }
           tr(213);
           // every warp of the quarter must have read D1 before any of them overwrites its low columns
           if (CS > 1) asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "n"(CS * 32) : "memory");
@@ -390,7 +395,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
         }
         // ---- epilogue 2: x_new = D2 -> XR[t] (raw) and XA (lrelu), or the stage output
         {
-          mbar_wait_relaxed(&bars.d2_full[t], ph);
+          mbar_wait(&bars.d2_full[t], ph);
           tc_fence_after();
           tr(220);
           uint32_t v[CW];
@@ -401,8 +406,10 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           if (!last || head) {
             if (!last) {
               // the 1x1 MMAs of this tile have retired: both accumulators may take the next block's biases
-              init_acc(tlane, s_bias[blk + 1][0]);
-              init_acc(tlane + CP, s_bias[blk + 1][1]);
+              if (!DBG(16)) {
+                init_acc(tlane, s_bias[blk + 1][0]);
+                init_acc(tlane + CP, s_bias[blk + 1][1]);
+              }
             } else {
               uint32_t bv[16];
 #pragma unroll
@@ -412,8 +419,10 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
             if (!last && !DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+            if (!DBG(32)) {
 #pragma unroll
-            for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
+              for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
+            }
             tr(224);
             put_xa(w);
             tr(225);
@@ -461,7 +470,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
       }
       if (head) {
         // ---- epilogue 3: tanh of the head accumulator -> fp32 [batch][head_ch][L]
-        mbar_wait_relaxed(&bars.d1_full[t], n_d1++ & 1);
+        mbar_wait(&bars.d1_full[t], n_d1++ & 1);
         tc_fence_after();
         uint32_t v[16];
         tmem_ld16_nw(tlane, v);
