@@ -120,6 +120,7 @@ def longform_inference(generator, mel, group=None, halo=None, infer_fn=None, gat
     send = torch.zeros((B, 1, longest), dtype=torch.float32, device=dev)
     if mine is not None:
         send[..., :mine.shape[-1]] = mine
-    recv = torch.empty((world, B, 1, longest), dtype=torch.float32, device=dev)
+    recv = torch.empty((world * B, 1, longest), dtype=torch.float32, device=dev)   # rank-major along dim 0
     dist.all_gather_into_tensor(recv, send, group=group)
+    recv = recv.view(world, B, 1, longest)
     return torch.cat([recv[r, ..., :(pe - ps) * hop] for r, (ps, pe) in enumerate(parts) if pe > ps], dim=-1)
