@@ -45,6 +45,8 @@ namespace {
 
 constexpr int TAPS = 3;
 constexpr int MAX_KT = TC_STACK_MAX_KT;
+constexpr int RING_KB = 32;        // channels per streamed weight chunk (ring mode)
+constexpr int RING_MAX_SLOTS = 12;
 
 
 #ifdef TTSB_STACK_TRACE
@@ -57,6 +59,7 @@ struct Bars {
   uint64_t x_full[2], x_free[2];
   uint64_t w1_full[TC_STACK_MAX_BLOCKS], w2_full[TC_STACK_MAX_BLOCKS], w1_free, w2_free, wh_full;
   uint64_t xa_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
+  uint64_t ring_full[RING_MAX_SLOTS], ring_empty[RING_MAX_SLOTS];
 };
 
 template <int CP, int KT, int CS>
@@ -72,6 +75,13 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
   static_assert(KT * TCOLS <= 512, "TMEM budget");
   constexpr uint32_t TMEM_ALLOC = KT * TCOLS <= 128 ? 128 : KT * TCOLS <= 256 ? 256 : 512;   // <= 256: two CTAs share an SM
   static_assert(CW % 8 == 0, "CP must be a multiple of 16");
+  // Ring mode (wide stages, one tile per CTA): a block's weights do not fit in shared memory, so they stream
+  // through a ring of [RING_KB channels x CP columns] chunks in exactly the order the MMAs consume them.
+  constexpr bool RING = CP > 96;
+  static_assert(!RING || KT == 1, "ring mode handles one tile per CTA");
+  constexpr int NK = CP / RING_KB;                       // chunks per tap
+  constexpr uint32_t SLOT_BYTES = RING_KB * CP * 2;
+  constexpr int NCH = (TAPS + 2) * NK;                   // chunks per block
 
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) Bars bars;
@@ -89,10 +99,10 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
   const uint32_t plane_bytes = (uint32_t)RS * 16;
   const uint32_t xa_bytes = (uint32_t)PL * plane_bytes;
   constexpr uint32_t W1_BYTES = TAPS * CP * CP * 2, W2_BYTES = 2 * CP * CP * 2;
-  const int wsets = p.w_sets;  // nb: every block's weights stay resident; 1: reloaded per block
+  const int wsets = p.w_sets;  // nb: every block's weights stay resident; 1: reloaded per block; ring mode: slots
   uint8_t* sXA = smem;
   uint8_t* sW = smem + 2 * xa_bytes;   // [set][W1 | W2S]
-  uint8_t* sWH = sW + (size_t)wsets * (W1_BYTES + W2_BYTES);   // head weights [taps][CP/8][16][8]
+  uint8_t* sWH = sW + (RING ? (size_t)wsets * SLOT_BYTES : (size_t)wsets * (W1_BYTES + W2_BYTES));   // head weights
   const uint32_t wh_bytes = head ? (uint32_t)p.head_taps * CP * 16 * 2 : 0;
 
   const int n_items = p.n_chains * p.batch;
@@ -109,6 +119,10 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
     mbar_init(&bars.w1_free, 1);
     mbar_init(&bars.w2_free, 1);
     mbar_init(&bars.wh_full, 1);
+    for (int i = 0; i < RING_MAX_SLOTS; ++i) {
+      mbar_init(&bars.ring_full[i], 1);
+      mbar_init(&bars.ring_empty[i], 1);
+    }
     for (int t = 0; t < KT; ++t) {
       mbar_init(&bars.xa_ready[t], GROUP_THREADS);
       mbar_init(&bars.d1_full[t], 1);
@@ -154,6 +168,19 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
       int gb = 0;
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
         for (int blk = 0; blk < nb; ++blk, ++gb) {
+          if (RING) {
+            for (int ch = 0; ch < NCH; ++ch) {
+              const uint32_t gc = (uint32_t)gb * NCH + ch;          // global chunk counter
+              const int slot = gc % wsets;
+              mbar_wait(&bars.ring_empty[slot], ((gc / wsets) & 1) ^ 1);
+              mbar_expect_tx(&bars.ring_full[slot], SLOT_BYTES);
+              const __nv_bfloat16* src = ch < TAPS * NK ? p.w1[blk] + (size_t)ch * (SLOT_BYTES / 2)
+                                                        : p.w2s[blk] + (size_t)(ch - TAPS * NK) * (SLOT_BYTES / 2);
+              bulk_g2s(sW + (size_t)slot * SLOT_BYTES, src, SLOT_BYTES, &bars.ring_full[slot]);
+              if (blk == 0 && ch == 0) load_x(it + 1);
+            }
+            continue;
+          }
           if (wsets == 1 || it == 0) {
             const int set = wsets == 1 ? 0 : blk;
             uint8_t* w1 = sW + (size_t)set * (W1_BYTES + W2_BYTES);
@@ -191,6 +218,55 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           const uint32_t w1 = smem_u32(sW + (size_t)set * (W1_BYTES + W2_BYTES)), w2 = w1 + W1_BYTES;
           const int d = p.dil[blk];
           // ---- dilated conv: D1[t] = sum_tap XA[rows + (tap-1) d] W1[tap]^T
+          if (RING) {
+            mbar_wait(&bars.xa_ready[0], n_xa & 1);
+            tc_fence_after();
+            uint32_t gc = (uint32_t)gb * NCH;
+            for (int j = 0; j < TAPS; ++j) {
+              const uint32_t a_row = xa + (uint32_t)(G + (j - 1) * d) * 16;
+              for (int kc = 0; kc < NK; ++kc, ++gc) {
+                const int slot = gc % wsets;
+                mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
+                tc_fence_after();
+                if (leader) {
+                  const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
+#pragma unroll
+                  for (int kk = 0; kk < RING_KB / 16; ++kk)
+                    umma_bf16(tbase, a_tmpl | (uint64_t)((a_row + (uint32_t)(kc * (RING_KB / 8) + 2 * kk) * lbo_a) >> 4),
+                              b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
+                  umma_commit(&bars.ring_empty[slot]);
+                }
+                __syncwarp();
+              }
+            }
+            ++n_xa;
+            if (leader) {
+              umma_commit(&bars.d1_full[0]);
+              if (blk == nb - 1 && !head) umma_commit(&bars.x_free[buf]);
+            }
+            __syncwarp();
+            // ---- 1x1 conv on h + 1x1 shortcut on raw x, both A operands in TMEM
+            mbar_wait(&bars.h_ready[0], ph);
+            tc_fence_after();
+            for (int sx = 0; sx < 2; ++sx)
+              for (int kc = 0; kc < NK; ++kc, ++gc) {
+                const int slot = gc % wsets;
+                mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
+                tc_fence_after();
+                if (leader) {
+                  const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
+                  const uint32_t acol = tbase + (sx ? 2 * CP : 0) + 8 * (kc * (RING_KB / 16));
+#pragma unroll
+                  for (int kk = 0; kk < RING_KB / 16; ++kk)
+                    umma_bf16_ts(tbase + CP, acol + 8 * kk, b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
+                  umma_commit(&bars.ring_empty[slot]);
+                }
+                __syncwarp();
+              }
+            if (leader) umma_commit(&bars.d2_full[0]);
+            __syncwarp();
+            continue;
+          }
           if (wsets == 1) mbar_wait(&bars.w1_full[0], ph);
           else if (it == 0) mbar_wait(&bars.w1_full[set], 0);
 #pragma unroll 1
@@ -490,7 +566,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
   if (warp == PRODUCER_WARP) tmem_dealloc(tbase, TMEM_ALLOC);
 }
 
-constexpr size_t SMEM_MAX = 227 * 1024 - 6 * 1024;   // static: barriers + bias table (<= 4*2*96*4 B)
+constexpr size_t SMEM_MAX = 227 * 1024 - 8 * 1024;   // static: barriers + bias tables (<= 4*2*192*4 B)
 
 template <int CP, int KT, int CS>
 cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
@@ -507,6 +583,8 @@ int tc_stack_ctas_per_sm(int cp) { return tc_stack_kt(cp) * 5 * cp / 2 <= 256 ? 
 
 int tc_stack_kt(int cp) {
   switch (cp) {
+    case 192: return 1;
+    case 128: return 1;
     case 96: return 2;
     case 64: return 3;
     case 48: return 2;
@@ -538,6 +616,14 @@ bool tc_stack_configure(TcStackParams& p) {
   const size_t wh = head ? (size_t)p.head_taps * p.cp * 16 * 2 : 0;
   // two CTAs per SM when the TMEM footprint allows it: each then gets half of the shared memory
   const size_t budget = tc_stack_ctas_per_sm(p.cp) == 2 ? SMEM_MAX / 2 - 1024 : SMEM_MAX;
+  if (p.cp > 96) {   // ring mode: w_sets = number of [RING_KB x cp] chunk slots
+    if (head) return false;
+    const size_t slot = (size_t)RING_KB * p.cp * 2;
+    if (xa + 4 * slot > budget) return false;
+    const size_t n = (budget - xa) / slot;
+    p.w_sets = (int)(n > RING_MAX_SLOTS ? RING_MAX_SLOTS : n);
+    return true;
+  }
   if (xa + wset + wh > budget) return false;
   p.w_sets = xa + p.nblocks * wset + wh <= budget ? p.nblocks : 1;
   return true;
@@ -546,6 +632,7 @@ bool tc_stack_configure(TcStackParams& p) {
 cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream);
 
 size_t tc_stack_smem_bytes(const TcStackParams& p) {
+  if (p.cp > 96) return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * RING_KB * p.cp * 2;
   return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
          (p.head_w ? (size_t)p.head_taps * p.cp * 16 * 2 : 0);
 }
@@ -573,6 +660,8 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
 
 cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
   switch (p.cp) {
+    case 192: return launch<192, 1, 4>(p, smem, grid, stream);
+    case 128: return launch<128, 1, 4>(p, smem, grid, stream);
     case 96: return launch<96, 2, 2>(p, smem, grid, stream);
     case 64: return launch<64, 3, 1>(p, smem, grid, stream);
     case 48: return launch<48, 2, 1>(p, smem, grid, stream);
