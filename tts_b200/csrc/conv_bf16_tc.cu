@@ -317,15 +317,24 @@ SmemPlan smem_plan(const TcConvParams& p) {
   if (p.nsrc > 1) s.a_bytes += (size_t)p.src[1].planes * p.src[1].rows * 16;
   int nmax = 0;
   for (int g = 0; g < p.ngroups; ++g) nmax = nmax > p.grp[g].ncols ? nmax : p.grp[g].ncols;
-  static const int opts[][2] = {{64, 4}, {64, 3}, {32, 4}, {32, 3}, {32, 2}, {16, 3}, {16, 2}};
-  for (size_t budget : {SMEM_HALF, SMEM_MAX})
-    for (auto& o : opts) {
-      const size_t tot = s.a_bytes + (size_t)o[1] * (o[0] / 8) * nmax * 16;
-      if (tot <= budget) {
-        s.kb_stage = o[0]; s.nst = o[1]; s.total = tot;
-        return s;
-      }
+  // {channels per stage, stages}.  Sharing the SM is only worth it with a ring deep enough to cover the L2
+  // latency (>= 3 stages of >= 32 channels); otherwise one CTA per SM with the deepest ring that fits.
+  static const int half_opts[][2] = {{64, 4}, {64, 3}, {32, 4}, {32, 3}};
+  static const int full_opts[][2] = {{64, 4}, {64, 3}, {32, 4}, {32, 3}, {32, 2}, {16, 3}, {16, 2}};
+  for (auto& o : half_opts) {
+    const size_t tot = s.a_bytes + (size_t)o[1] * (o[0] / 8) * nmax * 16;
+    if (tot <= SMEM_HALF) {
+      s.kb_stage = o[0]; s.nst = o[1]; s.total = tot;
+      return s;
     }
+  }
+  for (auto& o : full_opts) {
+    const size_t tot = s.a_bytes + (size_t)o[1] * (o[0] / 8) * nmax * 16;
+    if (tot <= SMEM_MAX) {
+      s.kb_stage = o[0]; s.nst = o[1]; s.total = tot;
+      return s;
+    }
+  }
   s.total = (size_t)-1;
   return s;
 }
