@@ -147,7 +147,7 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
 
 // Fused-stack configuration for stage s; kt == 0 when the stage must use the per-conv kernels.  With
 // `with_head` the output head (LeakyReLU, ReflectionPad1d, Conv1d, Tanh) is folded into the last stage's kernel.
-TcStackParams stack_tiling(const ttsb200_plan* plan, int s, bool with_head = false) {
+TcStackParams stack_tiling(const ttsb200_plan* plan, int s, bool with_head = false, bool with_up = false) {
   const ttsb200_generator_config& cfg = plan->cfg;
   TcStackParams q{};
   q.cp = pad16(plan->stages[s].Cout);
@@ -162,8 +162,23 @@ TcStackParams stack_tiling(const ttsb200_plan* plan, int s, bool with_head = fal
     q.head_taps = cfg.proj_kernel;
     q.head_ch = cfg.out_channels;
   }
+  if (with_up) {   // the next stage's ConvTranspose1d rides on this stack
+    const StagePlan& nx = plan->stages[s + 1];
+    const TcGroupPlan& g = nx.tc_up.groups[0];
+    q.up_w = plan->blob16 + g.w_off;
+    q.up_b = plan->blob + g.bias_off;
+    q.up_f = nx.f;
+    q.up_P = nx.P;
+    q.up_n = g.ncols;
+  }
   if (!tc_stack_configure(q)) q.kt = 0;
   return q;
+}
+// Stage s's stack can also run stage s+1's transposed conv when all its columns fit one accumulator.
+bool up_fusable(const ttsb200_plan* plan, int s) {
+  if (s + 1 >= plan->cfg.n_stages || plan->cfg.num_res_blocks < 1) return false;
+  if (plan->stages[s + 1].tc_up.groups.size() != 1) return false;
+  return stack_tiling(plan, s, false, true).kt > 0;
 }
 // The head rides on the last stage's fused kernel when that kernel exists, the head fits its N = 16 tile and
 // no per-layer taps were asked for (the stack output is then never materialised).
@@ -287,13 +302,15 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     if (int rc = tap(1, cur, cfg.base_channels, sh.L0, true)) return rc;
   }
   int64_t Lin = sh.L0;
-  bool head_done = false;
+  bool head_done = false, up_done = false;
   for (int s = 0; s < S; ++s) {
     const StagePlan& sp = plan->stages[s];
     const int64_t L = sh.L[s];
     const int C = sp.Cout;
     const bool last_stage = s == S - 1;
-    {
+    if (up_done) {
+      up_done = false;   // the previous stage's stack already produced this stage's input in `cur`
+    } else {
       TcConvParams p = base(sp.tc_up, Lin + 1);               // GEMM rows q = 0..Lin
       p.up_P = sp.P;
       p.src[0] = src(cur, sp.Cin, Lin, 2, -1, 0, false);      // taps read x[q], x[q - 1] (zero rows at -1 and Lin)
@@ -309,7 +326,8 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     }
     const int half = (cfg.res_kernel - 1) / 2;
     const bool fuse_head = last_stage && a->n_taps == 0 && head_fusable(plan);
-    TcStackParams q = stack_tiling(plan, s, fuse_head);
+    const bool fuse_up = !last_stage && a->n_taps == 0 && up_fusable(plan, s);
+    TcStackParams q = stack_tiling(plan, s, fuse_head, fuse_up);
     if (q.kt > 0) {  // whole ResidualStack in one kernel
       const CanonDims din = canon_dims(plan, C, L);
       q.x = cur; q.x_batch_stride = (int64_t)din.elems; q.x_plane_rows = din.rows; q.x_halo = halo;
@@ -331,8 +349,16 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         bytes = 2.0 * B * C * L + 4.0 * B * cfg.out_channels * L;
         head_done = true;
       }
-      TTSB_CUDA(ln.run(fuse_head ? "bf16.resstack.fused+head" : "bf16.resstack.fused", sp.layer_stack, 2 * macs, bytes,
-                       [&] { return tc_stack_launch(q, B, st); }));
+      if (fuse_up) {
+        const StagePlan& nx = plan->stages[s + 1];
+        const CanonDims dn = canon_dims(plan, nx.Cout, sh.L[s + 1]);
+        q.up_out = TcCanonOut{nxt, (int64_t)dn.elems, dn.rows, halo, (int)sh.L[s + 1], 0, 0};
+        macs += 2.0 * nx.f * C * nx.Cout * L * B;
+        bytes = 2.0 * B * (C * L + (double)nx.Cout * sh.L[s + 1]);
+        up_done = true;
+      }
+      TTSB_CUDA(ln.run(fuse_head ? "bf16.resstack.fused+head" : fuse_up ? "bf16.resstack.fused+convT" : "bf16.resstack.fused",
+                       sp.layer_stack, 2 * macs, bytes, [&] { return tc_stack_launch(q, B, st); }));
       std::swap(cur, nxt);
     } else
     for (int bi = 0; bi < nb; ++bi) {

@@ -62,7 +62,9 @@ struct Bars {
   uint64_t ring_full[RING_MAX_SLOTS], ring_empty[RING_MAX_SLOTS];
 };
 
-template <int CP, int KT, int CS>
+// TAIL: what follows the last block — 0 the stack output is stored, 1 fused output head, 2 fused transposed conv
+// of the next stage.  A template parameter so each variant carries (and allocates registers for) its own code only.
+template <int CP, int KT, int CS, int TAIL>
 __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ? 2 : 1)
     tc_stack_kernel(const __grid_constant__ TcStackParams p) {
   constexpr int NT = 64 + KT * CS * 128;
@@ -88,11 +90,18 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float s_bias[TC_STACK_MAX_BLOCKS][2][CP];
   __shared__ __align__(16) float s_bias_head[16];
+  __shared__ __align__(16) float s_bias_up[256];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = p.guard, RS = TR + 2 * G;
-  const bool head = CS == 1 && p.head_w != nullptr;
-  const int hh = head ? (p.head_taps - 1) / 2 : 0;      // halo of the fused head conv
+  constexpr bool head = TAIL == 1;
+  constexpr bool up = TAIL == 2;                        // fused transposed conv of the next stage
+  constexpr bool tail = head || up;                     // one more MMA round on lrelu(x_out) after the last block
+  static_assert(!head || CS == 1, "the fused head has no channel split");
+  static_assert(!up || !RING, "ring mode has no fused transposed conv");
+  const int hh = head ? (p.head_taps - 1) / 2 : up ? 1 : 0;   // halo of the fused tail conv
+  const int UW = p.up_n / CS;                           // tail-conv columns per epilogue thread
+  const uint32_t up_bytes = up ? (uint32_t)2 * CP * p.up_n * 2 : 0;
   const int V = TR - 2 * (p.sum_d + hh);
   const int SD = p.sum_d + hh;                          // rows recomputed per chain side
   const int nb = p.nblocks;
@@ -138,6 +147,8 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
     s_bias[blk][r / CP][r % CP] = r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP];
   }
   if (head && tid < 16) s_bias_head[tid] = p.head_b[tid];
+  if (up)
+    for (int e = tid; e < p.up_n; e += NT) s_bias_up[e] = p.up_b[e];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -164,8 +175,19 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
       if (head) {
         mbar_expect_tx(&bars.wh_full, wh_bytes);
         bulk_g2s(sWH, p.head_w, wh_bytes, &bars.wh_full);
+      } else if (up && p.up_mode == 1) {   // tail weights resident for the life of the CTA
+        mbar_expect_tx(&bars.wh_full, up_bytes);
+        bulk_g2s(sWH, p.up_w, up_bytes, &bars.wh_full);
       }
+      const bool up_stream = up && p.up_mode == 2;   // tail weights take turns with W2S in its slot
+      auto load_up = [&](uint32_t& n_w2) {
+        mbar_wait(&bars.w2_free, (n_w2 - 1) & 1);
+        mbar_expect_tx(&bars.w2_full[0], up_bytes);
+        bulk_g2s(sW + W1_BYTES, p.up_w, up_bytes, &bars.w2_full[0]);
+        ++n_w2;
+      };
       int gb = 0;
+      uint32_t n_w2 = 0;   // loads issued into the streamed W2S slot (blocks, plus the fused transposed conv)
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
         for (int blk = 0; blk < nb; ++blk, ++gb) {
           if (RING) {
@@ -187,13 +209,17 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
             if (wsets == 1 && gb > 0) mbar_wait(&bars.w1_free, (gb - 1) & 1);
             mbar_expect_tx(&bars.w1_full[set], W1_BYTES);
             bulk_g2s(w1, p.w1[blk], W1_BYTES, &bars.w1_full[set]);
-            if (wsets == 1 && gb > 0) mbar_wait(&bars.w2_free, (gb - 1) & 1);
+            // the previous item's tail weights go in behind this item's first W1, so that load is never held up
+            if (up_stream && blk == 0 && it > 0) load_up(n_w2);
+            if (wsets == 1 && n_w2 > 0) mbar_wait(&bars.w2_free, (n_w2 - 1) & 1);
             mbar_expect_tx(&bars.w2_full[set], W2_BYTES);
             bulk_g2s(w1 + W1_BYTES, p.w2s[blk], W2_BYTES, &bars.w2_full[set]);
+            ++n_w2;
           }
           if (blk == 0) load_x(it + 1);   // prefetch the next item's tile behind this item's first weights
         }
       }
+      if (up_stream && n_w2 > 0) load_up(n_w2);   // tail weights of this CTA's last item
     }
   } else if (warp == MMA_WARP) {
     // =============================== MMA issuer ===============================
@@ -208,7 +234,8 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
       const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
       Tracer tr = make_tracer(p.trace, 0, leader);
       int gb = 0;
-      uint32_t n_xa = 0;   // completed xa_ready rounds (one per block, plus one per item with a fused head)
+      uint32_t n_xa = 0;   // completed xa_ready rounds (one per block, plus one per item with a fused tail conv)
+      uint32_t n_w2 = 0;   // consumed fills of the streamed W2S slot
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
         const int buf = it & 1;
         const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
@@ -242,7 +269,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
             ++n_xa;
             if (leader) {
               umma_commit(&bars.d1_full[0]);
-              if (blk == nb - 1 && !head) umma_commit(&bars.x_free[buf]);
+              if (blk == nb - 1 && !tail) umma_commit(&bars.x_free[buf]);
             }
             __syncwarp();
             // ---- 1x1 conv on h + 1x1 shortcut on raw x, both A operands in TMEM
@@ -294,15 +321,18 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           ++n_xa;
           if (leader) {
             if (wsets == 1) umma_commit(&bars.w1_free);
-            if (blk == nb - 1 && !head) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
+            if (blk == nb - 1 && !tail) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
           }
           __syncwarp();
+          tr(112);
           // ---- 1x1 conv on h (TMEM) + 1x1 shortcut on raw x (TMEM): D2[t]
-          if (wsets == 1) mbar_wait(&bars.w2_full[0], ph);
+          if (wsets == 1) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
           else if (it == 0) mbar_wait(&bars.w2_full[set], 0);
+          tr(113);
 #pragma unroll 1
           for (int t = 0; t < KT; ++t) {
             mbar_wait(&bars.h_ready[t], ph);
+            tr(116 + t);
             tc_fence_after();
             tr(120 + t);
             const uint32_t tcol = tbase + t * TCOLS;
@@ -350,6 +380,43 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           if (leader) umma_commit(&bars.x_free[buf]);
           __syncwarp();
         }
+        if (up) {
+          // ---- fused transposed conv of the next stage: D[t][0:N] = a[q] Wu[0]^T + a[q-1] Wu[1]^T, a = lrelu(x_out)
+          const int N = p.up_n;
+          const uint32_t idesc_u = make_idesc_bf16(128, N);
+          const uint32_t lbo_u = (uint32_t)N * 16;
+          const uint64_t bu_tmpl = make_desc(0, lbo_u, 128);
+          const bool resident = p.up_mode == 1;
+          const uint32_t wu = smem_u32(resident ? sWH : sW + W1_BYTES);
+          if (!resident) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
+          else if (it == 0) mbar_wait(&bars.wh_full, 0);
+#pragma unroll 1
+          for (int t = 0; t < KT; ++t) {
+            if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
+            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
+            tc_fence_after();
+            tr(140 + t);
+            if (leader) {
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                const uint32_t a_row = xa + (uint32_t)(G + t * 128 - j) * 16;
+                const uint32_t w_tap = wu + (uint32_t)j * (uint32_t)(CP * N * 2);
+#pragma unroll
+                for (int kk = 0; kk < KS; ++kk)
+                  umma_bf16(tbase + t * TCOLS, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
+                            bu_tmpl | (uint64_t)((w_tap + 2 * kk * lbo_u) >> 4), idesc_u, 1);
+              }
+              umma_commit(&bars.d1_full[t]);
+            }
+            __syncwarp();
+          }
+          ++n_xa;
+          if (leader) {
+            if (!resident) umma_commit(&bars.w2_free);
+            umma_commit(&bars.x_free[buf]);
+          }
+          __syncwarp();
+        }
       }
     }
   } else {
@@ -365,6 +432,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
     const int L = p.L;
     const int pair_bar = 1 + t * 4 + q4;        // named barrier shared by the CS warps of a quarter
     Tracer tr = make_tracer(p.trace, 1 + t, m == 0 && cs == 0);
+    Tracer trw = make_tracer(p.trace, 1 + KT + warp, lane == 0);   // per-warp arrival times
     uint32_t n_d1 = 0;                          // completed d1_full rounds (blocks, plus the fused head)
 
     int gb = 0;
@@ -400,6 +468,21 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
         if (tau >= 1 && tau <= G && -tau - g0 >= -G) row_store(-tau - g0, w);
         const int back = L - 1 - tau;
         if (back >= 1 && back <= G && L - 1 + back - g0 < TR + G) row_store(L - 1 + back - g0, w);
+      };
+      // Tail transposed conv: no mirrors — the rows either side of the sequence are its zero padding.
+      auto put_xa_up = [&](const uint32_t* w) {
+        if (!edge) {
+          row_store(t * 128 + m, w);
+          return;
+        }
+        const int tau = g0 + t * 128 + m;
+        if (tau < 0 || tau >= L) return;
+        row_store(tau - g0, w);
+        uint32_t z[CW / 2];
+#pragma unroll
+        for (int i = 0; i < CW / 2; ++i) z[i] = 0;
+        if (tau == 0) row_store(-1 - g0, z);
+        if (tau == L - 1) row_store(L - g0, z);
       };
       // Accumulators start from the bias: D[t] <- bias row, then every MMA accumulates (no FADD in the epilogues).
       auto init_acc = [&](uint32_t taddr, const float* bias_row) {
@@ -446,6 +529,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           mbar_wait(&bars.d1_full[t], n_d1++ & 1);
           tc_fence_after();
           tr(210);
+          trw(310);
           uint32_t v[CW];
           tmem_ld_nw<CW>(tlane + c0, v);
           tmem_wait_ld();
@@ -468,29 +552,38 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           tc_fence_before();
           mbar_arrive(&bars.h_ready[t]);
           tr(211);
+          trw(311);
         }
         // ---- epilogue 2: x_new = D2 -> XR[t] (raw) and XA (lrelu), or the stage output
         {
           mbar_wait(&bars.d2_full[t], ph);
           tc_fence_after();
           tr(220);
+          trw(320);
           uint32_t v[CW];
           tmem_ld_nw<CW>(tlane + CP + c0, v);
           tmem_wait_ld();
           tr(223);
           uint32_t w[CW / 2];
-          if (!last || head) {
+          if (!last || tail) {
             if (!last) {
               // the 1x1 MMAs of this tile have retired: both accumulators may take the next block's biases
               if (!DBG(16)) {
                 init_acc(tlane, s_bias[blk + 1][0]);
                 init_acc(tlane + CP, s_bias[blk + 1][1]);
               }
-            } else {
+            } else if (head) {
               uint32_t bv[16];
 #pragma unroll
               for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_head[i]);
               tmem_st<16>(tlane, bv);            // head accumulator <- head bias
+            } else {
+              for (int c = cs * UW; c < (cs + 1) * UW; c += 16) {   // transposed-conv accumulator <- its bias
+                uint32_t bv[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_up[c + i]);
+                tmem_st<16>(tlane + c, bv);
+              }
             }
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
@@ -500,7 +593,8 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
               for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
             }
             tr(224);
-            put_xa(w);
+            if (last && up) put_xa_up(w);
+            else put_xa(w);
             tr(225);
             tmem_wait_st();
             if (!DBG(8)) fence_proxy_async();
@@ -508,6 +602,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
             tc_fence_before();
             mbar_arrive(&bars.xa_ready[t]);
             tr(221);
+            trw(321);
           } else {
             const int tau = g0 + t * 128 + m;
             const bool own = tau >= chain * V && tau < (chain + 1) * V && tau < L;
@@ -559,6 +654,44 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
             if (i < p.head_ch) of[(int64_t)i * L] = tanhf(__uint_as_float(v[i]));
         }
       }
+      if (up) {
+        // ---- epilogue 3: transposed-conv accumulator -> next stage's input; GEMM row q holds output rows
+        // q f - P .. q f - P + f - 1, columns ordered [plane][phase][8]
+        mbar_wait(&bars.d1_full[t], n_d1++ & 1);
+        tc_fence_after();
+        tr(230);
+        const int tau = g0 + t * 128 + m;
+        const bool own = tau >= chain * V && tau < (chain + 1) * V && tau <= L;   // row L: x[L-1] w[r+f] tail
+        const TcCanonOut& o = p.up_out;
+        const int f = p.up_f;
+        const int n0 = tau * f - p.up_P;
+        // column unit u (8 channels) = (plane u / f, phase u % f): walk (plane, phase) and the store pointer together
+        int pl = (cs * UW / 8) / f, phi = (cs * UW / 8) - pl * f;
+        __nv_bfloat16* optr = o.base + (int64_t)b * o.batch_stride + ((int64_t)pl * o.plane_rows + o.halo + n0 + phi) * 8;
+        const int64_t wrap = ((int64_t)o.plane_rows - (f - 1)) * 8;
+        const bool interior = own && n0 >= 0 && n0 + f <= o.L;   // every phase of this row lands inside the output
+        for (int c = cs * UW; c < (cs + 1) * UW; c += 16) {
+          uint32_t v[16];
+          tmem_ld16_nw(tlane + c, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (interior || (own && n0 + phi >= 0 && n0 + phi < o.L))
+              *reinterpret_cast<uint4*>(optr) = make_uint4(
+                  pack_bf16x2(__uint_as_float(v[8 * h]), __uint_as_float(v[8 * h + 1])),
+                  pack_bf16x2(__uint_as_float(v[8 * h + 2]), __uint_as_float(v[8 * h + 3])),
+                  pack_bf16x2(__uint_as_float(v[8 * h + 4]), __uint_as_float(v[8 * h + 5])),
+                  pack_bf16x2(__uint_as_float(v[8 * h + 6]), __uint_as_float(v[8 * h + 7])));
+            if (++phi == f) {
+              phi = 0;
+              optr += wrap;
+            } else {
+              optr += 8;
+            }
+          }
+        }
+        tr(231);
+      }
     }
   }
   tc_fence_before();
@@ -568,9 +701,9 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
 
 constexpr size_t SMEM_MAX = 227 * 1024 - 8 * 1024;   // static: barriers + bias tables (<= 4*2*192*4 B)
 
-template <int CP, int KT, int CS>
+template <int CP, int KT, int CS, int TAIL>
 cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
-  auto kern = tc_stack_kernel<CP, KT, CS>;
+  auto kern = tc_stack_kernel<CP, KT, CS, TAIL>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
   if (e != cudaSuccess) return e;
   kern<<<grid, 64 + KT * CS * 128, smem, stream>>>(p);
@@ -580,6 +713,8 @@ cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t s
 }  // namespace
 
 int tc_stack_ctas_per_sm(int cp) { return tc_stack_kt(cp) * 5 * cp / 2 <= 256 ? 2 : 1; }
+
+int tc_stack_cs(int cp) { return cp >= 128 ? 4 : cp == 96 ? 2 : 1; }
 
 int tc_stack_kt(int cp) {
   switch (cp) {
@@ -608,7 +743,16 @@ bool tc_stack_configure(TcStackParams& p) {
   const bool head = p.head_w != nullptr;
   if (head && (p.cp > 64 || p.head_taps < 1 || p.head_taps > TC_MAX_TAPS || p.head_taps % 2 == 0 || p.head_ch > 16))
     return false;
-  const int hh = head ? (p.head_taps - 1) / 2 : 0;
+  const bool up = p.up_w != nullptr;
+  if (up) {
+    // the tail conv's accumulator overlays D1|D2, its weights take the streamed W1 slot, and with a channel
+    // split it must stay clear of the partner warp's D2 columns
+    const int cs = tc_stack_cs(p.cp), n = p.up_n;
+    if (head || p.cp > 96 || n < 16 || n > 256 || n % (16 * cs) || n > 2 * p.cp || (cs > 1 && n > p.cp) ||
+        p.up_f < 1 || n % (8 * p.up_f))
+      return false;
+  }
+  const int hh = head ? (p.head_taps - 1) / 2 : up ? 1 : 0;
   if (hh > p.guard) p.guard = (hh + 7) / 8 * 8;
   if (p.kt * 128 - 2 * (p.sum_d + hh) < 32 || p.guard + p.sum_d + hh > 127) return false;
   const size_t xa = 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;
@@ -625,7 +769,13 @@ bool tc_stack_configure(TcStackParams& p) {
     return true;
   }
   if (xa + wset + wh > budget) return false;
-  p.w_sets = xa + p.nblocks * wset + wh <= budget ? p.nblocks : 1;
+  p.w_sets = (!up && xa + p.nblocks * wset + wh <= budget) ? p.nblocks : 1;
+  if (up) {   // tail weights: resident beside the streamed block weights when they fit, else sharing the W2S slot
+    const size_t wu = (size_t)2 * p.cp * p.up_n * 2;
+    if (xa + wset + wu <= budget) p.up_mode = 1;
+    else if (p.up_n <= p.cp) p.up_mode = 2;
+    else return false;
+  }
   return true;
 }
 
@@ -634,7 +784,8 @@ cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t
 size_t tc_stack_smem_bytes(const TcStackParams& p) {
   if (p.cp > 96) return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * RING_KB * p.cp * 2;
   return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
-         (p.head_w ? (size_t)p.head_taps * p.cp * 16 * 2 : 0);
+         (p.head_w ? (size_t)p.head_taps * p.cp * 16 * 2 : 0) +
+         (p.up_w && p.up_mode == 1 ? (size_t)2 * p.cp * p.up_n * 2 : 0);
 }
 
 cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t stream) {
@@ -642,9 +793,9 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
   if (p.kt != tc_stack_kt(p.cp) || p.kt == 0) return cudaErrorInvalidConfiguration;
   const size_t smem = tc_stack_smem_bytes(p);
   if (smem > SMEM_MAX) return cudaErrorInvalidConfiguration;
-  const int V = p.kt * 128 - 2 * (p.sum_d + (p.head_w ? (p.head_taps - 1) / 2 : 0));
+  const int V = p.kt * 128 - 2 * (p.sum_d + (p.head_w ? (p.head_taps - 1) / 2 : p.up_w ? 1 : 0));
   p.batch = batch;
-  p.n_chains = ceil_div(p.L, V);
+  p.n_chains = ceil_div(p.L + (p.up_w ? 1 : 0), V);   // the transposed conv also has GEMM row L
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -659,15 +810,24 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
 }
 
 cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
-  switch (p.cp) {
-    case 192: return launch<192, 1, 4>(p, smem, grid, stream);
-    case 128: return launch<128, 1, 4>(p, smem, grid, stream);
-    case 96: return launch<96, 2, 2>(p, smem, grid, stream);
-    case 64: return launch<64, 3, 1>(p, smem, grid, stream);
-    case 48: return launch<48, 2, 1>(p, smem, grid, stream);
-    case 32: return launch<32, 2, 1>(p, smem, grid, stream);
-    default: return cudaErrorInvalidConfiguration;
-  }
+  const int tail = p.head_w ? 1 : p.up_w ? 2 : 0;
+#define TTSB_STACK_CASE(CP, KT, CS, TAIL) \
+  if (p.cp == CP && tail == TAIL) return launch<CP, KT, CS, TAIL>(p, smem, grid, stream)
+  TTSB_STACK_CASE(192, 1, 4, 0);
+  TTSB_STACK_CASE(128, 1, 4, 0);
+  TTSB_STACK_CASE(96, 2, 2, 0);
+  TTSB_STACK_CASE(96, 2, 2, 2);
+  TTSB_STACK_CASE(64, 3, 1, 0);
+  TTSB_STACK_CASE(64, 3, 1, 1);
+  TTSB_STACK_CASE(64, 3, 1, 2);
+  TTSB_STACK_CASE(48, 2, 1, 0);
+  TTSB_STACK_CASE(48, 2, 1, 1);
+  TTSB_STACK_CASE(48, 2, 1, 2);
+  TTSB_STACK_CASE(32, 2, 1, 0);
+  TTSB_STACK_CASE(32, 2, 1, 1);
+  TTSB_STACK_CASE(32, 2, 1, 2);
+#undef TTSB_STACK_CASE
+  return cudaErrorInvalidConfiguration;
 }
 
 }  // namespace ttsb

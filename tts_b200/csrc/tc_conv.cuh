@@ -100,6 +100,14 @@ struct TcStackParams {
   const float* head_b;           // [16]
   int head_taps, head_ch;        // kernel size (odd, <= TC_MAX_TAPS), real output channels (<= 16)
   float* head_out;               // fp32 [batch][head_ch][L]
+  // Optional fused ConvTranspose1d of the NEXT stage (melgan_generator.py:47-56): the stack output (activated,
+  // still in shared memory) is contracted with the two-tap polyphase weights, y[q f - P + r] = a[q] w[r] +
+  // a[q-1] w[r+f], and the kernel writes the next stage's input instead of its own output.
+  const __nv_bfloat16* up_w;     // [2 taps][cp/8][up_n][8], columns ordered [plane][phase][8]; nullptr = none
+  const float* up_b;             // [up_n]
+  int up_f, up_P, up_n;          // stride, output offset (padding), GEMM columns = f * C_next_pad
+  int up_mode;                   // filled by tc_stack_configure: 1 weights resident, 2 streamed through the W2S slot
+  TcCanonOut up_out;             // raw input of the next stage's stack (no margins), L = next length
   int debug;               // knock-out bits for timeline experiments (trace builds only)
   long long* trace;        // optional (TTSB200_STACK_TRACE): [role][256] {tag, clock} pairs written by CTA 0
   TcCanonOut out;
@@ -107,6 +115,7 @@ struct TcStackParams {
 };
 int tc_stack_ctas_per_sm(int cp);                 // 2 when two CTAs' accumulators fit the 512 TMEM columns
 int tc_stack_kt(int cp);                          // 0: this channel count has no fused kernel
+int tc_stack_cs(int cp);                          // epilogue warps per TMEM lane quarter (channel split)
 bool tc_stack_configure(TcStackParams& p);        // fills kt / sum_d / guard / w_sets from cp, dil[], nblocks
 size_t tc_stack_smem_bytes(const TcStackParams& p);
 cudaError_t tc_stack_launch(const TcStackParams& p, int batch, cudaStream_t stream);

@@ -566,6 +566,9 @@ int32_t ttsb200_launch_count(const ttsb200_plan* plan, int32_t precision, int32_
   for (int s = 0; s < S; ++s)
     launches += (precision == TTSB200_BF16 && n > 0 && stack_tiling(plan, s).kt > 0) ? 1 : 2 * n;
   if (precision == TTSB200_BF16 && n > 0 && head_fusable(plan)) --launches;   // head folded into the last stack
+  if (precision == TTSB200_BF16)
+    for (int s = 0; s + 1 < S; ++s)
+      if (up_fusable(plan, s)) --launches;   // next stage's transposed conv folded into this stack
   return launches + (precision == TTSB200_BF16 ? 1 : 0);
 }
 
