@@ -203,12 +203,46 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
     const float slope = p.slope;
     // rows that also own halo rows of the output (mirror / zero margins) are rare: test once per thread
     const bool near_edge = row0 <= halo || row0 + f - 1 >= out_L - 1 - halo;
+    // Even-stride transposed conv, interior row: units (plane, r), (plane, r + 1) are adjacent output rows, so a
+    // pair goes out as one 32-byte store (the host keeps halo - P even, which makes the address 32-byte aligned).
+    // 16-byte stores at a stride of f rows leave every sector half written per instruction and crawl.
+    const bool paired = to_canon && (f & 1) == 0 && ((halo - p.up_P) & 1) == 0 && row_ok && !near_edge;
     for (int c = hf * 32; c < ncols; c += 64) {
       const int nc = min(32, ncols - c);     // 16 or 32
       uint32_t v[32];
       tmem_ld16_nw(trow + c, v);
       if (nc > 16) tmem_ld16_nw(trow + c + 16, v + 16);
       tmem_wait_ld();
+      if (paired) {
+#pragma unroll
+        for (int u = 0; u < 4; u += 2) {
+          if (u * 8 < nc) {
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float y0 = __uint_as_float(v[u * 8 + 2 * i]), y1 = __uint_as_float(v[u * 8 + 2 * i + 1]);
+              if (act) {
+                y0 = lrelu_f(y0, slope);
+                y1 = lrelu_f(y1, slope);
+              }
+              w[i] = pack_bf16x2(y0, y1);
+            }
+            st_global_v8(ob + ((int64_t)plane * p.out_plane_rows + halo + row0 + r) * 8, w);
+            r += 2;
+            if (r == f) {
+              r = 0;
+              ++plane;
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)              // skip the partner warp's batch
+          if (++r == f) {
+            r = 0;
+            ++plane;
+          }
+        continue;
+      }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {          // 8-column units: one (plane, phase) each
         if (u * 8 < nc) {

@@ -178,6 +178,8 @@ TcStackParams stack_tiling(const ttsb200_plan* plan, int s, bool with_head = fal
 bool up_fusable(const ttsb200_plan* plan, int s) {
   if (s + 1 >= plan->cfg.n_stages || plan->cfg.num_res_blocks < 1) return false;
   if (plan->stages[s + 1].tc_up.groups.size() != 1) return false;
+  // the fused kernel writes a margin-free tensor: its consumer must be the next stage's fused stack
+  if (stack_tiling(plan, s + 1).kt == 0) return false;
   return stack_tiling(plan, s, false, true).kt > 0;
 }
 // The head rides on the last stage's fused kernel when that kernel exists, the head fits its N = 16 tile and
@@ -275,11 +277,11 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, st); }));
     return 0;
   };
-  auto tap = [&](int layer, const __nv_bfloat16* x, int C, int64_t L, bool undo) -> int {
+  auto tap = [&](int layer, const __nv_bfloat16* x, int C, int64_t L, bool undo, int x_halo) -> int {
     for (int i = 0; i < a->n_taps; ++i)
       if (a->tap_layers[i] == layer) {
         const CanonDims d = canon_dims(plan, C, L);
-        TTSB_CUDA(tc_untile_launch(x, B, C, L, d.planes, d.rows, halo, undo, slope, a->tap_out[i], st));
+        TTSB_CUDA(tc_untile_launch(x, B, C, L, d.planes, d.rows, x_halo, undo, slope, a->tap_out[i], st));
       }
     return 0;
   };
@@ -299,10 +301,11 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
                      (double)B * (cfg.in_channels + cfg.base_channels) * sh.L0 +
                          (double)cfg.proj_kernel * cfg.in_channels * cfg.base_channels))
       return rc;
-    if (int rc = tap(1, cur, cfg.base_channels, sh.L0, true)) return rc;
+    if (int rc = tap(1, cur, cfg.base_channels, sh.L0, true, halo)) return rc;
   }
   int64_t Lin = sh.L0;
   bool head_done = false, up_done = false;
+  int cur_halo = halo;   // plane row of sequence row 0 in `cur` (a fused transposed conv may shift it by one)
   for (int s = 0; s < S; ++s) {
     const StagePlan& sp = plan->stages[s];
     const int64_t L = sh.L[s];
@@ -317,12 +320,16 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       // consumer: block 0 (raw x + reflect) or, with no blocks, the next transposed conv / head
       if (nb > 0) canon_out(p, nxt, C, L, false, 1);
       else canon_out(p, nxt, C, L, true, last_stage ? 1 : 2);
+      // a fused stack reads its input at any row offset: shift by a row where that makes the transposed conv's
+      // output-row pairs 32-byte aligned (conv_bf16_tc.cu epilogue)
+      if (nb > 0 && sp.f % 2 == 0 && stack_tiling(plan, s).kt > 0) p.out_halo = halo + ((halo - sp.P) & 1);
+      cur_halo = p.out_halo;
       const double macs = 2.0 * sp.f * sp.Cin * C * Lin * B;
       if (int rc = run("bf16.upsample.convT", sp.layer_up, p, macs,
                        (double)B * (sp.Cin * Lin + C * L) + 2.0 * sp.f * sp.Cin * C))
         return rc;
       std::swap(cur, nxt);
-      if (int rc = tap(sp.layer_up, cur, C, L, nb == 0)) return rc;
+      if (int rc = tap(sp.layer_up, cur, C, L, nb == 0, cur_halo)) return rc;
     }
     const int half = (cfg.res_kernel - 1) / 2;
     const bool fuse_head = last_stage && a->n_taps == 0 && head_fusable(plan);
@@ -330,7 +337,8 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     TcStackParams q = stack_tiling(plan, s, fuse_head, fuse_up);
     if (q.kt > 0) {  // whole ResidualStack in one kernel
       const CanonDims din = canon_dims(plan, C, L);
-      q.x = cur; q.x_batch_stride = (int64_t)din.elems; q.x_plane_rows = din.rows; q.x_halo = halo;
+      q.x = cur; q.x_batch_stride = (int64_t)din.elems; q.x_plane_rows = din.rows; q.x_halo = cur_halo;
+      cur_halo = halo;
       q.L = (int)L; q.slope = slope;
       for (int bi = 0; bi < nb; ++bi) {
         const BlockPlan& bp = sp.blocks[bi];
@@ -352,7 +360,9 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       if (fuse_up) {
         const StagePlan& nx = plan->stages[s + 1];
         const CanonDims dn = canon_dims(plan, nx.Cout, sh.L[s + 1]);
-        q.up_out = TcCanonOut{nxt, (int64_t)dn.elems, dn.rows, halo, (int)sh.L[s + 1], 0, 0};
+        // rows q f - P .. of one GEMM row go out as 32-byte stores: keep (halo - P) even
+        cur_halo = halo + ((halo - nx.P) & 1);
+        q.up_out = TcCanonOut{nxt, (int64_t)dn.elems, dn.rows, cur_halo, (int)sh.L[s + 1], 0, 0};
         macs += 2.0 * nx.f * C * nx.Cout * L * B;
         bytes = 2.0 * B * (C * L + (double)nx.Cout * sh.L[s + 1]);
         up_done = true;
@@ -387,7 +397,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       }
     }
     if (nb > 0)
-      if (int rc = tap(sp.layer_stack, cur, C, L, true)) return rc;
+      if (int rc = tap(sp.layer_stack, cur, C, L, true, halo)) return rc;
     Lin = L;
   }
   {

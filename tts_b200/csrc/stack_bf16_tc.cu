@@ -668,20 +668,30 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
         // column unit u (8 channels) = (plane u / f, phase u % f): walk (plane, phase) and the store pointer together
         int pl = (cs * UW / 8) / f, phi = (cs * UW / 8) - pl * f;
         __nv_bfloat16* optr = o.base + (int64_t)b * o.batch_stride + ((int64_t)pl * o.plane_rows + o.halo + n0 + phi) * 8;
-        const int64_t wrap = ((int64_t)o.plane_rows - (f - 1)) * 8;
         const bool interior = own && n0 >= 0 && n0 + f <= o.L;   // every phase of this row lands inside the output
+        // Even f with (halo - P) even (the host shifts the tensor's halo by a row if needed): the two units of a
+        // 16-column batch are rows n, n+1 of one plane at a 32-byte aligned address -> one 256-bit store, and a
+        // warp's stores tile a contiguous span (16-byte stores at a 32-byte stride crawl through the LSU).
+        const bool paired = (f & 1) == 0 && ((o.halo - p.up_P) & 1) == 0;
+        const int64_t wrap = ((int64_t)o.plane_rows - (f - 1)) * 8;
         for (int c = cs * UW; c < (cs + 1) * UW; c += 16) {
           uint32_t v[16];
           tmem_ld16_nw(tlane + c, v);
           tmem_wait_ld();
+          uint32_t w[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+          if (paired && interior) {
+            if (!DBG(256)) st_global_v8(optr, w);
+            phi += 2;
+            optr += phi == f ? wrap + 8 : 16;
+            if (phi == f) phi = 0;
+            continue;
+          }
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
-            if (interior || (own && n0 + phi >= 0 && n0 + phi < o.L))
-              *reinterpret_cast<uint4*>(optr) = make_uint4(
-                  pack_bf16x2(__uint_as_float(v[8 * h]), __uint_as_float(v[8 * h + 1])),
-                  pack_bf16x2(__uint_as_float(v[8 * h + 2]), __uint_as_float(v[8 * h + 3])),
-                  pack_bf16x2(__uint_as_float(v[8 * h + 4]), __uint_as_float(v[8 * h + 5])),
-                  pack_bf16x2(__uint_as_float(v[8 * h + 6]), __uint_as_float(v[8 * h + 7])));
+            if (own && n0 + phi >= 0 && n0 + phi < o.L)
+              *reinterpret_cast<uint4*>(optr) = make_uint4(w[4 * h], w[4 * h + 1], w[4 * h + 2], w[4 * h + 3]);
             if (++phi == f) {
               phi = 0;
               optr += wrap;
