@@ -392,8 +392,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           else if (it == 0) mbar_wait(&bars.wh_full, 0);
 #pragma unroll 1
           for (int t = 0; t < KT; ++t) {
-            if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
-            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
+            mbar_wait(&bars.xa_ready[t], n_xa & 1);   // taps reach back one row only: tile t needs tiles <= t
             tc_fence_after();
             tr(140 + t);
             if (leader) {
