@@ -13,6 +13,8 @@
 //
 // Warp roles (192 threads): warp 0 = copy producer + TMEM owner, warp 1 = MMA issuer (one
 // thread), warps 2..5 = LeakyReLU prologue in shared memory + epilogue (one TMEM lane quarter each).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "tc_conv.cuh"
@@ -26,6 +28,155 @@ namespace {
 
 constexpr int NT = 320;            // producer, MMA issuer, 8 epilogue warps (two per TMEM lane quarter)
 constexpr int EPI_THREADS = 256;
+
+// Accumulator columns [c, c + nc) of this warp's lanes <- bias row (the MMAs then always accumulate).
+__device__ __forceinline__ void bias_to_acc(uint32_t trow, int c, int nc, int ncols, const float* s_bias) {
+  uint32_t bv[32];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 f4 = *reinterpret_cast<const float4*>(&s_bias[min(c + 4 * i, ncols - 4)]);
+    bv[4 * i] = __float_as_uint(f4.x); bv[4 * i + 1] = __float_as_uint(f4.y);
+    bv[4 * i + 2] = __float_as_uint(f4.z); bv[4 * i + 3] = __float_as_uint(f4.w);
+  }
+  tmem_st<16>(trow + c, bv);
+  if (nc > 16) tmem_st<16>(trow + c + 16, bv + 16);
+}
+
+// Accumulator tile -> output tensor, for one epilogue warp: TMEM lane quarter q4 (rows t0 + q4*32 + lane), the
+// 32-column batches hf, hf+2, ... of group G.  REINIT: each batch is overwritten with the bias row as soon as it
+// has been read, ready for the next tile's MMAs (persistent kernel).
+template <bool REINIT>
+__device__ __forceinline__ void conv_epilogue(const TcConvParams& p, const TcGroup& G, uint32_t trow, int q4, int hf,
+                                              int lane, int t0, int b, const float* s_bias) {
+  const int ncols = G.ncols;
+  const int q = t0 + q4 * 32 + lane;       // GEMM row of this thread
+  const bool row_ok = q < p.Lt;
+  const int f = p.up_f;
+  const int row0 = q * f - p.up_P;         // output row of phase 0
+  __nv_bfloat16* ob = p.out_c + (int64_t)b * p.out_batch_stride;
+  // (plane, phase) of the first 8-column unit; advanced incrementally (no division in the loop)
+  int plane = ((G.col_first >> 3) + hf * 4) / f, r = ((G.col_first >> 3) + hf * 4) - plane * f;
+  const int out_L = p.out_L, halo = p.out_halo, margin = p.margin;
+  const bool to_canon = p.out_mode == 0, act = p.out_lrelu != 0;
+  const float slope = p.slope;
+  // rows that also own halo rows of the output (mirror / zero margins) are rare: test once per thread
+  const int reach = margin == 1 ? halo : 0;
+  const bool near_edge = row_ok && margin != 0 && (row0 <= reach || row0 + f - 1 >= out_L - 1 - reach);
+  const bool whole = row_ok && row0 >= 0 && row0 + f <= out_L;   // every phase of this row lands inside the output
+  // Even-stride transposed conv: units (plane, r), (plane, r + 1) are adjacent output rows, so a pair goes out as
+  // one 32-byte store (the host keeps halo - P even, which makes the address 32-byte aligned).  16-byte stores
+  // at a stride of f rows leave every sector half written per instruction and crawl.
+  const bool paired = (f & 1) == 0 && ((halo - p.up_P) & 1) == 0;
+  // one output row of one plane, plus the halo rows it owns near a sequence end
+  auto put_row = [&](int pl, int tau, uint4 w4) {
+    if (tau < 0 || tau >= out_L) return;
+    __nv_bfloat16* pb = ob + (int64_t)pl * p.out_plane_rows * 8;
+    *reinterpret_cast<uint4*>(pb + (int64_t)(halo + tau) * 8) = w4;
+  };
+  auto put_margins = [&](int pl, int tau, uint4 w4) {
+    if (tau < 0 || tau >= out_L) return;
+    __nv_bfloat16* pb = ob + (int64_t)pl * p.out_plane_rows * 8;
+    if (margin == 1) {         // halo rows mirror the interior (ReflectionPad1d of the consumer)
+      if (tau >= 1 && tau <= halo) *reinterpret_cast<uint4*>(pb + (int64_t)(halo - tau) * 8) = w4;
+      const int back = out_L - 1 - tau;
+      if (back >= 1 && back <= halo) *reinterpret_cast<uint4*>(pb + (int64_t)(halo + out_L - 1 + back) * 8) = w4;
+    } else if (margin == 2) {  // zero rows either side (transposed conv of the consumer)
+      const uint4 z = make_uint4(0, 0, 0, 0);
+      if (tau == 0) *reinterpret_cast<uint4*>(pb + (int64_t)(halo - 1) * 8) = z;
+      if (tau == out_L - 1) *reinterpret_cast<uint4*>(pb + (int64_t)(halo + out_L) * 8) = z;
+    }
+  };
+  for (int c = hf * 32; c < ncols; c += 64) {
+    const int nc = min(32, ncols - c);     // 16 or 32
+    uint32_t v[32];
+#ifdef TTSB_STACK_TRACE
+    if (p.debug & 4) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = i + lane;
+    } else
+#endif
+    {
+    tmem_ld16_nw(trow + c, v);
+    if (nc > 16) tmem_ld16_nw(trow + c + 16, v + 16);
+    tmem_wait_ld();
+    }
+#ifdef TTSB_STACK_TRACE
+    if (!(p.debug & 2))
+#endif
+    if (REINIT) bias_to_acc(trow, c, nc, ncols, s_bias);
+    if (to_canon) {
+      uint32_t w[16];
+      if (act) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          w[i] = pack_bf16x2(lrelu_f(__uint_as_float(v[2 * i]), slope), lrelu_f(__uint_as_float(v[2 * i + 1]), slope));
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+      }
+      if (paired) {
+#pragma unroll
+        for (int u = 0; u < 4; u += 2) {
+          if (u * 8 < nc) {
+            const int tau = row0 + r;
+            if (whole) {
+              st_global_v8(ob + ((int64_t)plane * p.out_plane_rows + halo + tau) * 8, w + 4 * u);
+            } else if (row_ok) {
+              put_row(plane, tau, make_uint4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]));
+              put_row(plane, tau + 1, make_uint4(w[4 * u + 4], w[4 * u + 5], w[4 * u + 6], w[4 * u + 7]));
+            }
+            if (near_edge) {
+              put_margins(plane, tau, make_uint4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]));
+              put_margins(plane, tau + 1, make_uint4(w[4 * u + 4], w[4 * u + 5], w[4 * u + 6], w[4 * u + 7]));
+            }
+            r += 2;
+            if (r == f) {
+              r = 0;
+              ++plane;
+            }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {          // 8-column units: one (plane, phase) each
+          if (u * 8 < nc) {
+            const uint4 w4 = make_uint4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
+            if (row_ok) put_row(plane, row0 + r, w4);
+            if (near_edge) put_margins(plane, row0 + r, w4);
+            if (++r == f) {
+              r = 0;
+              ++plane;
+            }
+          }
+        }
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u * 8 < nc) {
+          const int tau = row0 + r;
+          if (row_ok && tau >= 0 && tau < out_L) {
+            float* of = p.out_f + ((int64_t)b * p.cout_real + plane * 8) * out_L + tau;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              if (plane * 8 + i < p.cout_real) of[(int64_t)i * out_L] = tanhf(__uint_as_float(v[u * 8 + i]));
+          }
+          if (++r == f) {
+            r = 0;
+            ++plane;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)              // skip the partner warp's batch
+      if (++r == f) {
+        r = 0;
+        ++plane;
+      }
+    __syncwarp();   // edge lanes took other branches: reconverge before the next warp-wide tcgen05.ld
+  }
+}
 
 __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcConvParams p, const int kb_stage,
                                                       const int nst) {
@@ -156,18 +307,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
     Tracer tr = make_tracer(p.trace, 2, et == 0);
     tr(30);
     // the accumulator starts from the bias row, so the MMAs always accumulate and the epilogue has no add
-    for (int c = hf * 32; c < ncols; c += 64) {
-      const int nc = min(32, ncols - c);
-      uint32_t bv[32];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float4 f4 = *reinterpret_cast<const float4*>(&s_bias[min(c + 4 * i, ncols - 4)]);
-        bv[4 * i] = __float_as_uint(f4.x); bv[4 * i + 1] = __float_as_uint(f4.y);
-        bv[4 * i + 2] = __float_as_uint(f4.z); bv[4 * i + 3] = __float_as_uint(f4.w);
-      }
-      tmem_st<16>(trow + c, bv);
-      if (nc > 16) tmem_st<16>(trow + c + 16, bv + 16);
-    }
+    for (int c = hf * 32; c < ncols; c += 64) bias_to_acc(trow, c, min(32, ncols - c), ncols, s_bias);
     tmem_wait_st();
     if (need_lrelu) {
       const Slope2 slope2 = make_slope2(p.slope);
@@ -191,106 +331,7 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
     mbar_wait_relaxed(&bar_d, 0);
     tc_fence_after();
     tr(32);
-    const int q = t0 + q4 * 32 + lane;       // GEMM row of this thread
-    const bool row_ok = q < p.Lt;
-    const int f = p.up_f;
-    const int row0 = q * f - p.up_P;         // output row of phase 0
-    __nv_bfloat16* ob = p.out_c + (int64_t)b * p.out_batch_stride;
-    // (plane, phase) of the first 8-column unit; advanced incrementally (no division in the loop)
-    int plane = ((G.col_first >> 3) + hf * 4) / f, r = ((G.col_first >> 3) + hf * 4) - plane * f;
-    const int out_L = p.out_L, halo = p.out_halo, margin = p.margin;
-    const bool to_canon = p.out_mode == 0, act = p.out_lrelu != 0;
-    const float slope = p.slope;
-    // rows that also own halo rows of the output (mirror / zero margins) are rare: test once per thread
-    const bool near_edge = row0 <= halo || row0 + f - 1 >= out_L - 1 - halo;
-    // Even-stride transposed conv, interior row: units (plane, r), (plane, r + 1) are adjacent output rows, so a
-    // pair goes out as one 32-byte store (the host keeps halo - P even, which makes the address 32-byte aligned).
-    // 16-byte stores at a stride of f rows leave every sector half written per instruction and crawl.
-    const bool paired = to_canon && (f & 1) == 0 && ((halo - p.up_P) & 1) == 0 && row_ok && !near_edge;
-    for (int c = hf * 32; c < ncols; c += 64) {
-      const int nc = min(32, ncols - c);     // 16 or 32
-      uint32_t v[32];
-      tmem_ld16_nw(trow + c, v);
-      if (nc > 16) tmem_ld16_nw(trow + c + 16, v + 16);
-      tmem_wait_ld();
-      if (paired) {
-#pragma unroll
-        for (int u = 0; u < 4; u += 2) {
-          if (u * 8 < nc) {
-            uint32_t w[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              float y0 = __uint_as_float(v[u * 8 + 2 * i]), y1 = __uint_as_float(v[u * 8 + 2 * i + 1]);
-              if (act) {
-                y0 = lrelu_f(y0, slope);
-                y1 = lrelu_f(y1, slope);
-              }
-              w[i] = pack_bf16x2(y0, y1);
-            }
-            st_global_v8(ob + ((int64_t)plane * p.out_plane_rows + halo + row0 + r) * 8, w);
-            r += 2;
-            if (r == f) {
-              r = 0;
-              ++plane;
-            }
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u)              // skip the partner warp's batch
-          if (++r == f) {
-            r = 0;
-            ++plane;
-          }
-        continue;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {          // 8-column units: one (plane, phase) each
-        if (u * 8 < nc) {
-          const int tau = row0 + r;
-          if (row_ok && tau >= 0 && tau < out_L) {
-            float y[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) y[i] = __uint_as_float(v[u * 8 + i]);
-            if (to_canon) {
-              if (act) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) y[i] = lrelu_f(y[i], slope);
-              }
-              const uint4 w4 = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
-                                          pack_bf16x2(y[6], y[7]));
-              __nv_bfloat16* pb = ob + (int64_t)plane * p.out_plane_rows * 8;
-              *reinterpret_cast<uint4*>(pb + (int64_t)(halo + tau) * 8) = w4;
-              if (near_edge) {
-                if (margin == 1) {         // halo rows mirror the interior (ReflectionPad1d of the consumer)
-                  if (tau >= 1 && tau <= halo) *reinterpret_cast<uint4*>(pb + (int64_t)(halo - tau) * 8) = w4;
-                  const int back = out_L - 1 - tau;
-                  if (back >= 1 && back <= halo) *reinterpret_cast<uint4*>(pb + (int64_t)(halo + out_L - 1 + back) * 8) = w4;
-                } else if (margin == 2) {  // zero rows either side (transposed conv of the consumer)
-                  const uint4 z = make_uint4(0, 0, 0, 0);
-                  if (tau == 0) *reinterpret_cast<uint4*>(pb + (int64_t)(halo - 1) * 8) = z;
-                  if (tau == out_L - 1) *reinterpret_cast<uint4*>(pb + (int64_t)(halo + out_L) * 8) = z;
-                }
-              }
-            } else {
-              float* of = p.out_f + ((int64_t)b * p.cout_real + plane * 8) * out_L + tau;
-#pragma unroll
-              for (int i = 0; i < 8; ++i)
-                if (plane * 8 + i < p.cout_real) of[(int64_t)i * out_L] = tanhf(y[i]);
-            }
-          }
-          if (++r == f) {
-            r = 0;
-            ++plane;
-          }
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u)              // skip the partner warp's batch
-        if (++r == f) {
-          r = 0;
-          ++plane;
-        }
-    }
+    conv_epilogue<false>(p, G, trow, q4, hf, lane, t0, b, s_bias);
   }
   if (warp >= 2) {
     Tracer tr = make_tracer(p.trace, 3, tid == 64);
@@ -299,6 +340,148 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tbase, tcols);
+}
+
+// ---- persistent, weights-resident variant ---------------------------------------------------------------
+// For layers whose output is wide and whose K is deep (projection, transposed convs) the kernel above spends
+// most of its life streaming the same weights into every CTA and serialising load -> MMA -> epilogue.  Here a
+// CTA keeps ONE column group's weights in shared memory for its whole life and walks over (utterance, time
+// tile) units: activations stream through a ring of 64-channel chunks, two TMEM accumulators alternate, so the
+// loads of unit i+1, the MMAs of unit i and the epilogue of unit i-1 overlap.
+constexpr int CP_MAX_SLOTS = 6;
+constexpr int CP_CHUNK_PLANES = 8;   // 64 channels per activation chunk
+
+__global__ void __launch_bounds__(NT) tc_convp_kernel(const __grid_constant__ TcConvParams p, const int nslots,
+                                                       const int n_tiles, const int batch) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bar_w, a_full[CP_MAX_SLOTS], a_empty[CP_MAX_SLOTS], acc_full[2], acc_free[2];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float s_bias[256];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ngroups = p.ngroups;
+  const TcGroup& G = p.grp[blockIdx.x % ngroups];
+  const int ncols = G.ncols;
+  const TcSrc& S = p.src[0];
+  const int planes = S.planes, taps = S.taps;
+  const uint32_t lbo_a = (uint32_t)S.rows * 16;
+  const uint32_t slot_bytes = CP_CHUNK_PLANES * lbo_a;
+  const uint32_t tap_bytes = (uint32_t)planes * ncols * 16;
+  uint8_t* sW = smem;                               // [tap][plane][ncols][8]
+  uint8_t* sA = smem + (size_t)taps * tap_bytes;    // ring of [<= 8 planes][rows][8] chunks
+  const int nchunks = (planes + CP_CHUNK_PLANES - 1) / CP_CHUNK_PLANES;
+  const uint32_t acc_stride = ncols <= 32 ? 32 : ncols <= 64 ? 64 : ncols <= 128 ? 128 : 256;
+  const int first = blockIdx.x / ngroups, stride = gridDim.x / ngroups;
+  const int n_units = n_tiles * batch;
+
+  if (tid == 0) {
+    mbar_init(&bar_w, 1);
+    for (int s = 0; s < nslots; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_free[i], EPI_THREADS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc(&tmem_base_s, 2 * acc_stride);
+  for (int c = tid; c < ncols; c += NT) s_bias[c] = G.bias[c];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = tmem_base_s;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      mbar_expect_tx(&bar_w, (uint32_t)taps * tap_bytes);
+      for (int j = 0; j < taps; ++j)
+        bulk_g2s(sW + (size_t)j * tap_bytes, G.w + (size_t)j * (tap_bytes / 2), tap_bytes, &bar_w);
+      uint32_t gc = 0;
+      for (int u = first; u < n_units; u += stride) {
+        const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
+        const __nv_bfloat16* gx = S.x + (int64_t)b * S.batch_stride + (int64_t)(S.row_base + t0) * 8;
+        for (int c = 0; c < nchunks; ++c, ++gc) {
+          const int slot = gc % nslots;
+          mbar_wait(&a_empty[slot], ((gc / nslots) & 1) ^ 1);
+          const int npl = min(CP_CHUNK_PLANES, planes - c * CP_CHUNK_PLANES);
+          mbar_expect_tx(&a_full[slot], (uint32_t)npl * lbo_a);
+          for (int pl = 0; pl < npl; ++pl)
+            bulk_g2s(sA + (size_t)slot * slot_bytes + (size_t)pl * lbo_a,
+                     gx + (int64_t)(c * CP_CHUNK_PLANES + pl) * S.plane_rows * 8, lbo_a, &a_full[slot]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const bool leader = elect_one() != 0;
+    const uint32_t idesc = make_idesc_bf16(TC_TILE_M, ncols);
+    const uint32_t lbo_b = (uint32_t)ncols * 16;
+    const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, lbo_b, 128);
+    const uint32_t w_base = smem_u32(sW), a_base = smem_u32(sA);
+    Tracer tr = make_tracer(p.trace, 1, leader);
+    tr(19);
+    mbar_wait(&bar_w, 0);
+    tr(18);
+    uint32_t gc = 0;
+    int i = 0;
+    for (int u = first; u < n_units; u += stride, ++i) {
+      const int buf = i & 1;
+      mbar_wait(&acc_free[buf], (i >> 1) & 1);   // epilogue has drained this accumulator and reloaded the bias
+      tc_fence_after();
+      tr(20);
+      const uint32_t d = tbase + buf * acc_stride;
+      for (int c = 0; c < nchunks; ++c, ++gc) {
+        const int slot = gc % nslots;
+        mbar_wait(&a_full[slot], (gc / nslots) & 1);
+        tc_fence_after();
+        tr(22);
+        if (leader) {
+          const int npl = min(CP_CHUNK_PLANES, planes - c * CP_CHUNK_PLANES);
+          for (int j = 0; j < taps; ++j) {
+            uint32_t a_lo = (a_base + slot * slot_bytes + (uint32_t)S.tap_row[j] * 16) >> 4;
+            uint32_t b_lo = (w_base + j * tap_bytes + (uint32_t)(c * CP_CHUNK_PLANES) * lbo_b) >> 4;
+            for (int kk = 0; kk < npl / 2; ++kk) {
+              umma_bf16(d, a_tmpl | a_lo, b_tmpl | b_lo, idesc, 1);
+              a_lo += lbo_a >> 3;   // two planes further, in 16-byte units
+              b_lo += lbo_b >> 3;
+            }
+          }
+          umma_commit(&a_empty[slot]);
+        }
+        __syncwarp();
+      }
+      if (leader) umma_commit(&acc_full[buf]);
+      __syncwarp();
+      tr(21);
+    }
+  } else {
+    Tracer tr = make_tracer(p.trace, warp, lane == 0);
+    const int q4 = warp & 3, hf = (warp - 2) >> 2;
+    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
+    for (int buf = 0; buf < 2; ++buf)
+      for (int c = hf * 32; c < ncols; c += 64) bias_to_acc(trow + buf * acc_stride, c, min(32, ncols - c), ncols, s_bias);
+    tmem_wait_st();
+    tc_fence_before();
+    mbar_arrive(&acc_free[0]);
+    mbar_arrive(&acc_free[1]);
+    int i = 0;
+    for (int u = first; u < n_units; u += stride, ++i) {
+      const int buf = i & 1;
+      mbar_wait_relaxed(&acc_full[buf], (i >> 1) & 1);
+      tc_fence_after();
+      tr(30);
+      const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
+      conv_epilogue<true>(p, G, trow + buf * acc_stride, q4, hf, lane, t0, b, s_bias);
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(&acc_free[buf]);
+      tr(31);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tbase, 2 * acc_stride);
 }
 
 // ---- layout helpers --------------------------------------------------------------------------------
@@ -377,8 +560,52 @@ SmemPlan smem_plan(const TcConvParams& p) {
 // bytes of dynamic shared memory of the launch
 size_t tc_conv_smem_bytes(const TcConvParams& p) { return smem_plan(p).total; }
 
+namespace {
+// Ring depth of the persistent variant for this launch; 0 = not eligible (two sources, in-kernel LeakyReLU,
+// fp32 output, or weights that do not fit beside a useful ring).
+int convp_slots(const TcConvParams& p, size_t* smem_bytes) {
+  static const bool off = getenv("TTSB200_CONV_PERSISTENT") && atoi(getenv("TTSB200_CONV_PERSISTENT")) == 0;
+  if (off || p.nsrc != 1 || p.src[0].lrelu || p.out_mode != 0 || (p.src[0].planes & 1)) return 0;
+  size_t w = 0;
+  for (int g = 0; g < p.ngroups; ++g) {
+    if (p.grp[g].ncols > 256) return 0;
+    const size_t wg = (size_t)p.src[0].taps * p.src[0].planes * p.grp[g].ncols * 16;
+    w = w > wg ? w : wg;
+  }
+  const size_t slot = (size_t)CP_CHUNK_PLANES * p.src[0].rows * 16;
+  if (w + 2 * slot > SMEM_MAX) return 0;
+  size_t n = (SMEM_MAX - w) / slot;
+  const size_t nchunks = (p.src[0].planes + CP_CHUNK_PLANES - 1) / CP_CHUNK_PLANES;
+  if (n > CP_MAX_SLOTS) n = CP_MAX_SLOTS;
+  if (n > 2 * nchunks) n = 2 * nchunks;   // two whole tiles in flight is as deep as the pipeline gets
+  if (n < 2) n = 2;
+  *smem_bytes = w + n * slot;
+  return (int)n;
+}
+}  // namespace
+
 cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, cudaStream_t stream) {
   TcConvParams p = p_in;
+  {
+    size_t smem = 0;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int nslots = convp_slots(p, &smem);
+    if (nslots > 0 && p.ngroups <= sms) {
+      cudaError_t e = cudaFuncSetAttribute(tc_convp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+      if (e != cudaSuccess) return e;
+      const int n_tiles = ceil_div(p.Lt, TC_TILE_M);
+      int per_group = sms / p.ngroups;
+      if (per_group > n_tiles * batch) per_group = n_tiles * batch;
+      if (const char* dbg = getenv("TTSB200_CONV_DEBUG")) p.debug = atoi(dbg);
+      p.trace = trace_begin(stream);
+      tc_convp_kernel<<<per_group * p.ngroups, NT, smem, stream>>>(p, nslots, n_tiles, batch);
+      const cudaError_t rc = cudaGetLastError();
+      trace_end(p.trace, 1000 + p.trace_id, stream);
+      return rc;
+    }
+  }
   {  // per-device attribute; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
     if (e != cudaSuccess) return e;

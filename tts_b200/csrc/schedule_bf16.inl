@@ -23,7 +23,7 @@ inline int pad16(int c) { return (int)round_up(c, 16); }
 // wfun(src, tap, ci, phase, co) / bfun(co): reference weights; channels beyond the real counts are zero.
 template <class WF, class BF>
 int pack_tc_layer(Bf16Builder& b16, BlobBuilder& bb, TcLayer& L, int nsrc, const int* taps, const int* cin, int cout,
-                  int up_f, WF wfun, BF bfun) {
+                  int up_f, WF wfun, BF bfun, bool resident = false) {
   L.cin_pad = pad16(cin[0]);
   L.cout_pad = pad16(cout);
   L.cout = cout;
@@ -33,8 +33,16 @@ int pack_tc_layer(Bf16Builder& b16, BlobBuilder& bb, TcLayer& L, int nsrc, const
   int unit = 8 * up_f;                       // one plane
   while (unit % 16) unit *= 2;
   if (unit > 256) return fail(TTSB200_ERR_INVALID, "upsample factor too large for the BF16 path");
+  // `resident`: the layer runs on the persistent conv kernel, which keeps a whole group's weights in shared
+  // memory beside a ring of activation chunks (conv_bf16_tc.cu) — size the groups for that.
+  int cap = 256;
+  if (resident) {
+    const size_t w_budget = (size_t)(227 - 3) * 1024 - (size_t)4 * 8 * (128 + 24) * 16;
+    const size_t per_col = (size_t)taps[0] * pad16(cin[0]) * 2;
+    if (w_budget / per_col >= (size_t)unit) cap = (int)std::min<size_t>(256, w_budget / per_col);
+  }
   int ncols = unit;
-  for (int n = 256 / unit * unit; n >= unit; n -= unit)
+  for (int n = cap / unit * unit; n >= unit; n -= unit)
     if (total % n == 0) { ncols = n; break; }
   for (int col0 = 0; col0 < total; col0 += ncols) {
     TcGroupPlan g;
@@ -80,7 +88,7 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
     const int Cin = cfg.in_channels, k = cfg.proj_kernel;
     if (int rc = pack_tc_layer(b16, bb, plan->tc_proj, 1, taps, cin, cfg.base_channels, 1,
                                [&](int, int j, int ci, int, int co) { return w[((size_t)co * Cin + ci) * k + j]; },
-                               [&](int co) { return b[co]; }))
+                               [&](int co) { return b[co]; }, true))
       return rc;
     ti += 2;
   }
@@ -97,7 +105,7 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
                                  [&](int, int j, int ci, int ph, int co) {
                                    return w[((size_t)ci * Cout + co) * (2 * f) + ph + f * j];
                                  },
-                                 [&](int co) { return b[co]; }))
+                                 [&](int co) { return b[co]; }, true))
         return rc;
       ti += 2;
     }
@@ -318,7 +326,9 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       p.up_P = sp.P;
       p.src[0] = src(cur, sp.Cin, Lin, 2, -1, 0, false);      // taps read x[q], x[q - 1] (zero rows at -1 and Lin)
       // consumer: block 0 (raw x + reflect) or, with no blocks, the next transposed conv / head
-      if (nb > 0) canon_out(p, nxt, C, L, false, 1);
+      // consumer: the fused stack (mirrors its own edges: no margins), else block 0 (raw x + reflect) or, with
+      // no blocks, the next transposed conv / head
+      if (nb > 0) canon_out(p, nxt, C, L, false, stack_tiling(plan, s).kt > 0 ? 0 : 1);
       else canon_out(p, nxt, C, L, true, last_stage ? 1 : 2);
       // a fused stack reads its input at any row offset: shift by a row where that makes the transposed conv's
       // output-row pairs 32-byte aligned (conv_bf16_tc.cu epilogue)

@@ -34,7 +34,7 @@ struct TcGroup {
   int col_first;           // first layer column of the group
 };
 
-constexpr int TC_MAX_GROUPS = 16;
+constexpr int TC_MAX_GROUPS = 32;
 
 struct TcConvParams {
   TcSrc src[2];
@@ -57,6 +57,7 @@ struct TcConvParams {
   float slope;
   long long* trace;       // optional timeline buffer (trace.cuh)
   int trace_id;
+  int debug;              // knock-out bits for timeline experiments (trace builds only)
 };
 
 // Where a kernel's result goes: canonical bf16 for the next tcgen05 kernel (halo rows filled per the
