@@ -21,6 +21,31 @@ int fail(int code, const std::string& msg);
       return ::ttsb::fail(TTSB200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
   } while (0)
 
+// ---- programmatic dependent launch -------------------------------------------------------------------
+// The kernels of one inference run back to back on one stream.  Launched with the programmatic-serialization
+// attribute, kernel N+1 may start its preamble (barrier init, TMEM allocation, weight prefetch) while kernel N
+// drains; it calls pdl_wait() before touching anything kernel N wrote (or still reads).  pdl_wait() returns when
+// every prerequisite grid has completed and flushed, so chains of such kernels stay correctly ordered.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <class... KArgs, class... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 static inline int ceil_div(int64_t x, int64_t m) { return (int)((x + m - 1) / m); }
 

@@ -218,6 +218,8 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -392,12 +394,15 @@ __global__ void __launch_bounds__(NT) tc_convp_kernel(const __grid_constant__ Tc
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
+  pdl_launch_dependents();
+  if (warp != 0) pdl_wait();   // warp 0 first starts the weight load (weights are written by no kernel)
 
   if (warp == 0) {
     if (elect_one()) {
       mbar_expect_tx(&bar_w, (uint32_t)taps * tap_bytes);
       for (int j = 0; j < taps; ++j)
         bulk_g2s(sW + (size_t)j * tap_bytes, G.w + (size_t)j * (tap_bytes / 2), tap_bytes, &bar_w);
+      pdl_wait();
       uint32_t gc = 0;
       for (int u = first; u < n_units; u += stride) {
         const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
@@ -488,6 +493,8 @@ __global__ void __launch_bounds__(NT) tc_convp_kernel(const __grid_constant__ Tc
 __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int pad, __nv_bfloat16* __restrict__ out,
                                 int planes, int plane_rows, int halo) {
   // one thread per (plane row, plane); row index covers halo margins too (reflect of the padded signal)
+  pdl_launch_dependents();
+  pdl_wait();
   const int L = T + 2 * pad;
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   const int pl = blockIdx.y, b = blockIdx.z;
@@ -600,8 +607,8 @@ cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, cudaStream_t str
       if (per_group > n_tiles * batch) per_group = n_tiles * batch;
       if (const char* dbg = getenv("TTSB200_CONV_DEBUG")) p.debug = atoi(dbg);
       p.trace = trace_begin(stream);
-      tc_convp_kernel<<<per_group * p.ngroups, NT, smem, stream>>>(p, nslots, n_tiles, batch);
-      const cudaError_t rc = cudaGetLastError();
+      const cudaError_t rc =
+          launch_pdl(tc_convp_kernel, dim3(per_group * p.ngroups), dim3(NT), smem, stream, p, nslots, n_tiles, batch);
       trace_end(p.trace, 1000 + p.trace_id, stream);
       return rc;
     }
@@ -614,8 +621,7 @@ cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, cudaStream_t str
   if (sp.total > SMEM_MAX) return cudaErrorInvalidConfiguration;
   const dim3 grid(ceil_div(p.Lt, TC_TILE_M), p.ngroups, batch);
   p.trace = trace_begin(stream);
-  tc_conv_kernel<<<grid, NT, sp.total, stream>>>(p, sp.kb_stage, sp.nst);
-  const cudaError_t rc = cudaGetLastError();
+  const cudaError_t rc = launch_pdl(tc_conv_kernel, grid, dim3(NT), sp.total, stream, p, sp.kb_stage, sp.nst);
   trace_end(p.trace, 1000 + p.trace_id, stream);
   return rc;
 }

@@ -36,6 +36,7 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
   const int q0 = blockIdx.x * SQ_TILE;
   const float* xb = x + (int64_t)b * 4 * Ts;
 
+  pdl_launch_dependents();
   if (tid < 64) {
     const int k = tid >> 4, o = (tid & 15) - 7;
     float c[4];
@@ -46,6 +47,7 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
     }
     sc[k][tid & 15] = make_float4(c[0], c[1], c[2], c[3]);
   }
+  pdl_wait();   // the head's sub-band signals are complete from here on
   for (int e = tid; e < 4 * SQ_SMEM_Q; e += SQ_THREADS) {
     const int k = e / SQ_SMEM_Q, s = e - k * SQ_SMEM_Q;
     const int q = q0 - SQ_HALO_L + s;
@@ -155,7 +157,7 @@ cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int
   if (batch <= 0 || Ts <= 0 || Tout <= 0) return cudaSuccess;
   if (bands == 4 && taps == 62 && Ts < (1 << 30)) {
     const dim3 grid(ceil_div(Ts, SQ_TILE), batch);
-    pqmf_synth_4x63_kernel<<<grid, SQ_THREADS, 0, stream>>>(x, G, y, (int)Ts);
+    return launch_pdl(pqmf_synth_4x63_kernel, grid, dim3(SQ_THREADS), 0, stream, x, G, y, (int)Ts);
   } else {
     const dim3 grid(ceil_div(Tout, 256), batch);
     pqmf_synth_generic_kernel<<<grid, 256, 0, stream>>>(x, G, y, bands, K, pad, Ts, Tout);

@@ -153,6 +153,8 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
+  pdl_launch_dependents();
+  if (warp != PRODUCER_WARP) pdl_wait();   // the producer first prefetches weights (not written by any kernel)
 
   if (warp == PRODUCER_WARP) {
     // =============================== producer ===============================
@@ -171,7 +173,6 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           bulk_g2s(dst + (size_t)pl * plane_bytes, gx + (int64_t)pl * p.x_plane_rows * 8, (uint32_t)TR * 16,
                    &bars.x_full[buf]);
       };
-      load_x(0);
       if (head) {
         mbar_expect_tx(&bars.wh_full, wh_bytes);
         bulk_g2s(sWH, p.head_w, wh_bytes, &bars.wh_full);
@@ -179,6 +180,8 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
         mbar_expect_tx(&bars.wh_full, up_bytes);
         bulk_g2s(sWH, p.up_w, up_bytes, &bars.wh_full);
       }
+      pdl_wait();   // the previous kernel's output is complete from here on
+      load_x(0);
       const bool up_stream = up && p.up_mode == 2;   // tail weights take turns with W2S in its slot
       auto load_up = [&](uint32_t& n_w2) {
         mbar_wait(&bars.w2_free, (n_w2 - 1) & 1);
@@ -715,8 +718,7 @@ cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t s
   auto kern = tc_stack_kernel<CP, KT, CS, TAIL>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
   if (e != cudaSuccess) return e;
-  kern<<<grid, 64 + KT * CS * 128, smem, stream>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(kern, dim3(grid), dim3(64 + KT * CS * 128), smem, stream, p);
 }
 
 }  // namespace
