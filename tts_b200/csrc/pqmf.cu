@@ -18,9 +18,10 @@ namespace ttsb {
 namespace {
 
 // ---- specialised N=4, K=63 (the only PQMF the reference instantiates: multiband_melgan_generator.py:24)
-constexpr int SQ_THREADS = 128;
+constexpr int SQ_THREADS = 64;
 constexpr int SQ_QPT = 4;                        // q (groups of 4 outputs) per thread
-constexpr int SQ_TILE = SQ_THREADS * SQ_QPT;     // 512 q per CTA -> 2048 output samples
+constexpr int SQ_TILE = SQ_THREADS * SQ_QPT;     // 256 q per CTA -> 1024 output samples: small CTAs, several waves,
+                                                 // so one CTA's loads and stores hide behind another's FMAs
 constexpr int SQ_HALO_L = 8;                     // window is q-7..q+8; 8 keeps float4 alignment
 constexpr int SQ_SMEM_Q = SQ_TILE + 16;          // 8 left + 8 right
 
@@ -29,7 +30,6 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
                                                                       float* __restrict__ y, int Ts) {
   __shared__ __align__(16) float sx[4][SQ_SMEM_Q];
   __shared__ __align__(16) float4 sc[4][16];              // sc[k][off+7] = 4*G[k][4*off+31-r], r=0..3
-  __shared__ __align__(16) float so[SQ_THREADS * 16 + 16];
 
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
@@ -48,10 +48,22 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
     sc[k][tid & 15] = make_float4(c[0], c[1], c[2], c[3]);
   }
   pdl_wait();   // the head's sub-band signals are complete from here on
-  for (int e = tid; e < 4 * SQ_SMEM_Q; e += SQ_THREADS) {
-    const int k = e / SQ_SMEM_Q, s = e - k * SQ_SMEM_Q;
-    const int q = q0 - SQ_HALO_L + s;
-    sx[k][s] = (q >= 0 && q < Ts) ? __ldg(xb + (int64_t)k * Ts + q) : 0.f;
+  // window rows q0-8 .. q0+TILE+8 of the four bands; whole float4s when the rows allow it
+  const bool vec = (Ts & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+  if (vec) {
+    for (int e = tid; e < SQ_SMEM_Q; e += SQ_THREADS) {     // e = k * (SMEM_Q/4) + s4
+      const int k = e / (SQ_SMEM_Q / 4), s4 = e - k * (SQ_SMEM_Q / 4);
+      const int q = q0 - SQ_HALO_L + 4 * s4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (q >= 0 && q + 3 < Ts) v = __ldg(reinterpret_cast<const float4*>(xb + (int64_t)k * Ts + q));
+      *reinterpret_cast<float4*>(&sx[k][4 * s4]) = v;       // q < 0 or q >= Ts: zero padding (whole vectors)
+    }
+  } else {
+    for (int e = tid; e < 4 * SQ_SMEM_Q; e += SQ_THREADS) {
+      const int k = e / SQ_SMEM_Q, s = e - k * SQ_SMEM_Q;
+      const int q = q0 - SQ_HALO_L + s;
+      sx[k][s] = (q >= 0 && q < Ts) ? __ldg(xb + (int64_t)k * Ts + q) : 0.f;
+    }
   }
   __syncthreads();
 
@@ -81,26 +93,24 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
     }
   }
 
-  // stage 16 consecutive outputs per thread, then write full lines
-#pragma unroll
-  for (int i = 0; i < SQ_QPT; ++i)
-    *reinterpret_cast<float4*>(&so[tid * 16 + 4 * i]) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-  __syncthreads();
+  // each thread owns 4*QPT consecutive outputs, written as 32-byte stores (full sectors, no staging pass)
   const int64_t Tout = 4 * (int64_t)Ts;
-  float* yb = y + (int64_t)b * Tout + (int64_t)q0 * 4;
-  const int64_t remain = Tout - (int64_t)q0 * 4;  // multiple of 4
-  const bool aligned = (reinterpret_cast<uintptr_t>(y) & 15) == 0;
+  const int64_t t_first = (int64_t)(q0 + SQ_QPT * tid) * 4;
+  float* yt = y + (int64_t)b * Tout + t_first;
+  static_assert(SQ_QPT == 4, "the stores below write 16 floats per thread");
+  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int e = (tid + SQ_THREADS * i) * 4;
-    if (e < remain) {
-      const float4 v = *reinterpret_cast<const float4*>(&so[e]);
-      if (aligned) {
-        *reinterpret_cast<float4*>(yb + e) = v;
-      } else {
-        yb[e] = v.x; yb[e + 1] = v.y; yb[e + 2] = v.z; yb[e + 3] = v.w;
-      }
-    }
+    for (int h = 0; h < 2; ++h)
+      asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(yt + 8 * h), "f"(acc[2 * h][0]),
+                   "f"(acc[2 * h][1]), "f"(acc[2 * h][2]), "f"(acc[2 * h][3]), "f"(acc[2 * h + 1][0]),
+                   "f"(acc[2 * h + 1][1]), "f"(acc[2 * h + 1][2]), "f"(acc[2 * h + 1][3])
+                   : "memory");
+  } else {
+#pragma unroll
+    for (int i = 0; i < SQ_QPT; ++i)
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = acc[i][r];
   }
 }
 
