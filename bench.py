@@ -317,6 +317,90 @@ def gpu_arm(args):
         dist.destroy_process_group()
 
 
+def longform_arm(args):
+    """BASELINE config 4: ONE 10-minute utterance split along time across the ranks (tts_b200/longform.py)."""
+    from tts_b200 import longform
+    rank, world, local = dist_setup(args.gpus)
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    model = make_model(args.dtype).to(dev).eval()
+    model.freeze()
+    T = 51680
+    mel = torch.randn(1, 80, T, generator=torch.Generator().manual_seed(MEL_SEED)).to(dev)   # replicated: 16.5 MB
+    halo = longform.receptive_halo_frames(model)
+    n_out = (T + 2 * PAD) * longform.hop_length(model)
+    stream = torch.cuda.current_stream(dev)
+    for _ in range(args.warmup):
+        wav = longform.longform_inference(model, mel)
+    torch.cuda.synchronize(dev)
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        wav = longform.longform_inference(model, mel)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    barrier(world)
+    ms = allreduce_max(e0.elapsed_time(e1), world, dev)
+    assert wav.shape[-1] == n_out
+    value = n_out * args.steps / (ms / 1e3)
+    line = {"metric": "mb_melgan_pqmf_longform_audio_samples_per_s", "value": value, "unit": "samples/s",
+            "x_realtime": value / SAMPLE_RATE, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32" if args.dtype == "fp32" else "bf16", "data": "synthetic",
+            "config": {"workload": "BASELINE config 4: one 600 s utterance [1,80,51680] split along time over the "
+                                   f"ranks, {halo}-frame halo from the replicated mel (zero-byte exchange), "
+                                   "all_gather of the waveform slices", "frames": T, "halo_frames": halo,
+                       "parallelism": f"time split x{world}"}}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+def streaming_arm(args):
+    """BASELINE config 5: FB-MelGAN with hop 300 fed 250 ms chunks; per-chunk latency through the public API."""
+    from tts_b200.streaming import StreamingVocoder
+    from tts_b200.vocoder.models.fullband_melgan_generator import FullbandMelganGenerator
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    torch.manual_seed(WEIGHT_SEED)
+    m = FullbandMelganGenerator(upsample_factors=(5, 5, 4, 3))
+    m.remove_weight_norm()
+    m.inference_padding = PAD
+    m.precision = args.dtype
+    m = m.to(dev).eval()
+    m.freeze()
+    chunk, rate = 20, 24000
+    sv = StreamingVocoder(m, chunk_frames=chunk)
+    n_chunks = max(50, args.steps * 10)
+    mel = torch.randn(1, 80, chunk * (n_chunks + args.warmup + 4), generator=torch.Generator().manual_seed(MEL_SEED))
+    host = mel.pin_memory()
+    lat, samples = [], 0
+    for i in range(n_chunks + args.warmup + 4):
+        piece = host[..., i * chunk:(i + 1) * chunk]
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        outs = sv.feed(piece.to(dev, non_blocking=True))      # H2D of the chunk, window inference on the CUDA path
+        got = [o.cpu() for o in outs]                         # D2H of the emitted samples (blocking, like the server)
+        dt = time.perf_counter() - t0
+        if got and i >= args.warmup + 4:
+            lat.append(dt)
+            samples += sum(g.shape[-1] for g in got)
+    lat.sort()
+    p50, p99 = lat[len(lat) // 2], lat[min(len(lat) - 1, int(len(lat) * 0.99))]
+    line = {"metric": "fb_melgan_stream_chunk_latency_ms", "value": p50 * 1e3, "unit": "ms", "p99_ms": p99 * 1e3,
+            "x_realtime": (samples / rate) / sum(lat), "n_gpus": 1, "steps": len(lat), "warmup": args.warmup,
+            "ms_per_step": sum(lat) / len(lat) * 1e3, "higher_is_better": False, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32" if args.dtype == "fp32" else "bf16", "data": "synthetic",
+            "config": {"workload": "BASELINE config 5: FullbandMelganGenerator(upsample_factors=(5,5,4,3)) hop 300, "
+                                   f"24 kHz, stream of [1,80,{chunk}] chunks (250 ms), context {sv.ctx} frames per side, "
+                                   "latency = host chunk in -> 6000 samples back on the host",
+                       "chunk_frames": chunk, "context_frames": sv.ctx, "samples_per_chunk": chunk * sv.hop}}
+    print(json.dumps(line))
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -341,10 +425,16 @@ def main():
     ap.add_argument("--dtype", default=os.environ.get("TTSB200_BENCH_DTYPE", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="batched", choices=["batched", "longform", "streaming"],
+                    help="batched = BASELINE config 2 (the headline line); longform = config 4; streaming = config 5")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         reference_arm(args)
+    elif args.workload == "longform":
+        longform_arm(args)
+    elif args.workload == "streaming":
+        streaming_arm(args)
     else:
         gpu_arm(args)
 
