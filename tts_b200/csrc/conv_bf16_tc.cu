@@ -159,7 +159,7 @@ __device__ __forceinline__ void conv_epilogue(const TcConvParams& p, const TcGro
             float* of = p.out_f + ((int64_t)b * p.cout_real + plane * 8) * out_L + tau;
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-              if (plane * 8 + i < p.cout_real) of[(int64_t)i * out_L] = tanhf(__uint_as_float(v[u * 8 + i]));
+              if (plane * 8 + i < p.cout_real) of[(int64_t)i * out_L] = tanh_fast(__uint_as_float(v[u * 8 + i]));
           }
           if (++r == f) {
             r = 0;
@@ -352,8 +352,11 @@ __global__ void __launch_bounds__(NT) tc_conv_kernel(const __grid_constant__ TcC
 // loads of unit i+1, the MMAs of unit i and the epilogue of unit i-1 overlap.
 constexpr int CP_MAX_SLOTS = 6;
 constexpr int CP_CHUNK_PLANES = 8;   // 64 channels per activation chunk
+// A chunk is 8 small plane copies; their issue cost (~450 + 90 per copy cycles of the issuing warp, see
+// tests/cuda/ingest_probe.cu) exceeds the chunk's MMA time, so two warps issue alternate chunks.
+constexpr int NTP = NT + 32;
 
-__global__ void __launch_bounds__(NT) tc_convp_kernel(const __grid_constant__ TcConvParams p, const int nslots,
+__global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ TcConvParams p, const int nslots,
                                                        const int n_tiles, const int batch) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bar_w, a_full[CP_MAX_SLOTS], a_empty[CP_MAX_SLOTS], acc_full[2], acc_free[2];
@@ -389,7 +392,7 @@ __global__ void __launch_bounds__(NT) tc_convp_kernel(const __grid_constant__ Tc
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc(&tmem_base_s, 2 * acc_stride);
-  for (int c = tid; c < ncols; c += NT) s_bias[c] = G.bias[c];
+  for (int c = tid; c < ncols; c += NTP) s_bias[c] = G.bias[c];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -397,17 +400,22 @@ __global__ void __launch_bounds__(NT) tc_convp_kernel(const __grid_constant__ Tc
   pdl_launch_dependents();
   if (warp != 0) pdl_wait();   // warp 0 first starts the weight load (weights are written by no kernel)
 
-  if (warp == 0) {
+  constexpr int PRODUCER2 = NT / 32;   // the extra warp: odd activation chunks
+  if (warp == 0 || warp == PRODUCER2) {
     if (elect_one()) {
-      mbar_expect_tx(&bar_w, (uint32_t)taps * tap_bytes);
-      for (int j = 0; j < taps; ++j)
-        bulk_g2s(sW + (size_t)j * tap_bytes, G.w + (size_t)j * (tap_bytes / 2), tap_bytes, &bar_w);
-      pdl_wait();
+      const uint32_t mine = warp == 0 ? 0 : 1;
+      if (warp == 0) {
+        mbar_expect_tx(&bar_w, (uint32_t)taps * tap_bytes);
+        for (int j = 0; j < taps; ++j)
+          bulk_g2s(sW + (size_t)j * tap_bytes, G.w + (size_t)j * (tap_bytes / 2), tap_bytes, &bar_w);
+        pdl_wait();
+      }
       uint32_t gc = 0;
       for (int u = first; u < n_units; u += stride) {
         const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
         const __nv_bfloat16* gx = S.x + (int64_t)b * S.batch_stride + (int64_t)(S.row_base + t0) * 8;
         for (int c = 0; c < nchunks; ++c, ++gc) {
+          if ((gc & 1) != mine) continue;
           const int slot = gc % nslots;
           mbar_wait(&a_empty[slot], ((gc / nslots) & 1) ^ 1);
           const int npl = min(CP_CHUNK_PLANES, planes - c * CP_CHUNK_PLANES);
@@ -608,7 +616,7 @@ cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, cudaStream_t str
       if (const char* dbg = getenv("TTSB200_CONV_DEBUG")) p.debug = atoi(dbg);
       p.trace = trace_begin(stream);
       const cudaError_t rc =
-          launch_pdl(tc_convp_kernel, dim3(per_group * p.ngroups), dim3(NT), smem, stream, p, nslots, n_tiles, batch);
+          launch_pdl(tc_convp_kernel, dim3(per_group * p.ngroups), dim3(NTP), smem, stream, p, nslots, n_tiles, batch);
       trace_end(p.trace, 1000 + p.trace_id, stream);
       return rc;
     }

@@ -45,8 +45,12 @@ namespace {
 
 constexpr int TAPS = 3;
 constexpr int MAX_KT = TC_STACK_MAX_KT;
-constexpr int RING_KB = 32;        // channels per streamed weight chunk (ring mode)
+// Ring mode: channels per streamed weight chunk.  A bulk copy costs its issuing warp ~540 cycles however small it
+// is and only two are in flight per SM (tests/cuda/ingest_probe.cu: 12 KB chunks from one warp = 22 B/cycle/SM,
+// 24 KB chunks from two warps = 90), so chunks are as large as the ring allows and two warps issue them.
+constexpr int RING_KB = 64;
 constexpr int RING_MAX_SLOTS = 12;
+constexpr int ring_producers(int cp) { return cp > 96 ? 2 : 1; }
 
 
 #ifdef TTSB_STACK_TRACE
@@ -65,9 +69,9 @@ struct Bars {
 // TAIL: what follows the last block — 0 the stack output is stored, 1 fused output head, 2 fused transposed conv
 // of the next stage.  A template parameter so each variant carries (and allocates registers for) its own code only.
 template <int CP, int KT, int CS, int TAIL>
-__global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ? 2 : 1)
+__global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ? 2 : 1)
     tc_stack_kernel(const __grid_constant__ TcStackParams p) {
-  constexpr int NT = 64 + KT * CS * 128;
+  constexpr int NT = 32 + 32 * ring_producers(CP) + KT * CS * 128;
   constexpr int GROUP_THREADS = CS * 128;
   constexpr int PL = CP / 8;          // 8-channel planes
   constexpr int KS = CP / 16;         // K = 16 steps per tap
@@ -141,6 +145,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
     fence_mbar_init();
   }
   constexpr int PRODUCER_WARP = KT * CS * 4, MMA_WARP = PRODUCER_WARP + 1;
+  constexpr int PRODUCER2_WARP = MMA_WARP + 1;   // ring mode only: issues the odd weight chunks
   if (warp == PRODUCER_WARP) tmem_alloc(&tmem_base_s, TMEM_ALLOC);
   for (int e = tid; e < nb * 2 * CP; e += NT) {
     const int blk = e / (2 * CP), r = e - blk * 2 * CP;
@@ -196,13 +201,14 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           if (RING) {
             for (int ch = 0; ch < NCH; ++ch) {
               const uint32_t gc = (uint32_t)gb * NCH + ch;          // global chunk counter
+              if (blk == 0 && ch == 0) load_x(it + 1);
+              if (gc & 1) continue;                                 // odd chunks: the second producer warp
               const int slot = gc % wsets;
               mbar_wait(&bars.ring_empty[slot], ((gc / wsets) & 1) ^ 1);
               mbar_expect_tx(&bars.ring_full[slot], SLOT_BYTES);
               const __nv_bfloat16* src = ch < TAPS * NK ? p.w1[blk] + (size_t)ch * (SLOT_BYTES / 2)
                                                         : p.w2s[blk] + (size_t)(ch - TAPS * NK) * (SLOT_BYTES / 2);
               bulk_g2s(sW + (size_t)slot * SLOT_BYTES, src, SLOT_BYTES, &bars.ring_full[slot]);
-              if (blk == 0 && ch == 0) load_x(it + 1);
             }
             continue;
           }
@@ -223,6 +229,22 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
         }
       }
       if (up_stream && n_w2 > 0) load_up(n_w2);   // tail weights of this CTA's last item
+    }
+  } else if (RING && warp == PRODUCER2_WARP) {
+    // ================ second weight producer (ring mode): the odd chunks of the same sequence ================
+    if (elect_one()) {
+      for (int it = 0, gb = 0; blockIdx.x + it * gridDim.x < n_items; ++it)
+        for (int blk = 0; blk < nb; ++blk, ++gb)
+          for (int ch = 0; ch < NCH; ++ch) {
+            const uint32_t gc = (uint32_t)gb * NCH + ch;
+            if (!(gc & 1)) continue;
+            const int slot = gc % wsets;
+            mbar_wait(&bars.ring_empty[slot], ((gc / wsets) & 1) ^ 1);
+            mbar_expect_tx(&bars.ring_full[slot], SLOT_BYTES);
+            const __nv_bfloat16* src = ch < TAPS * NK ? p.w1[blk] + (size_t)ch * (SLOT_BYTES / 2)
+                                                      : p.w2s[blk] + (size_t)(ch - TAPS * NK) * (SLOT_BYTES / 2);
+            bulk_g2s(sW + (size_t)slot * SLOT_BYTES, src, SLOT_BYTES, &bars.ring_full[slot]);
+          }
     }
   } else if (warp == MMA_WARP) {
     // =============================== MMA issuer ===============================
@@ -299,16 +321,14 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           }
           if (wsets == 1) mbar_wait(&bars.w1_full[0], ph);
           else if (it == 0) mbar_wait(&bars.w1_full[set], 0);
-#pragma unroll 1
-          for (int t = 0; t < KT; ++t) {
-            if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
-            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
-            tc_fence_after();
-            tr(100 + t);
+          // Issue order: tap j of tile t reads rows shifted by (j - 1) d, so taps 0 and 1 need tiles <= t only and
+          // start as soon as tile t has been rewritten; tap 2 follows once tile t + 1 is there.  The last tile's
+          // epilogue 2 thereby overlaps the first two taps of the tiles before it.
+          auto issue_taps = [&](int t, int j0, int j1) {
             const uint32_t dcol = tbase + t * TCOLS;
             if (leader) {
 #pragma unroll
-              for (int j = 0; j < TAPS; ++j) {
+              for (int j = j0; j < j1; ++j) {
                 const uint32_t a_row = xa + (uint32_t)(G + t * 128 + (j - 1) * d) * 16;
                 const uint32_t w_tap = w1 + (uint32_t)j * (CP * CP * 2);
 #pragma unroll
@@ -316,11 +336,24 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
                   umma_bf16(dcol, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
                             b_tmpl | (uint64_t)((w_tap + 2 * kk * LBO_B) >> 4), idesc, 1);
               }
-              umma_commit(&bars.d1_full[t]);
             }
+          };
+#pragma unroll 1
+          for (int t = 0; t < KT; ++t) {
+            mbar_wait(&bars.xa_ready[t], n_xa & 1);
+            tc_fence_after();
+            tr(100 + t);
+            if (t > 0) {
+              issue_taps(t - 1, 2, 3);
+              if (leader) umma_commit(&bars.d1_full[t - 1]);
+            }
+            issue_taps(t, 0, 2);
             __syncwarp();
             tr(110 + t);
           }
+          issue_taps(KT - 1, 2, 3);
+          if (leader) umma_commit(&bars.d1_full[KT - 1]);
+          __syncwarp();
           ++n_xa;
           if (leader) {
             if (wsets == 1) umma_commit(&bars.w1_free);
@@ -328,10 +361,22 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           }
           __syncwarp();
           tr(112);
-          // ---- 1x1 conv on h (TMEM) + 1x1 shortcut on raw x (TMEM): D2[t]
+          // ---- D2[t] = S x (raw x in TMEM: ready since the previous round's epilogue 2, so these fill the wait for
+          // epilogue 1) + W2 h (h in TMEM, written by epilogue 1)
           if (wsets == 1) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
           else if (it == 0) mbar_wait(&bars.w2_full[set], 0);
           tr(113);
+          if (leader) {
+#pragma unroll 1
+            for (int t = 0; t < KT; ++t) {
+              const uint32_t tcol = tbase + t * TCOLS;
+#pragma unroll
+              for (int kk = 0; kk < KS; ++kk)
+                umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
+                             b_tmpl | (uint64_t)((w2 + CP * CP * 2 + 2 * kk * LBO_B) >> 4), idesc, 1);
+            }
+          }
+          __syncwarp();
 #pragma unroll 1
           for (int t = 0; t < KT; ++t) {
             mbar_wait(&bars.h_ready[t], ph);
@@ -343,10 +388,6 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
 #pragma unroll
               for (int kk = 0; kk < KS; ++kk)
                 umma_bf16_ts(tcol + CP, tcol + 8 * kk, b_tmpl | (uint64_t)((w2 + 2 * kk * LBO_B) >> 4), idesc, 1);
-#pragma unroll
-              for (int kk = 0; kk < KS; ++kk)
-                umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
-                             b_tmpl | (uint64_t)((w2 + CP * CP * 2 + 2 * kk * LBO_B) >> 4), idesc, 1);
               umma_commit(&bars.d2_full[t]);
             }
             __syncwarp();
@@ -653,7 +694,7 @@ __global__ void __launch_bounds__(64 + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ?
           float* of = p.head_out + (int64_t)b * p.head_ch * L + tau;
 #pragma unroll
           for (int i = 0; i < 16; ++i)
-            if (i < p.head_ch) of[(int64_t)i * L] = tanhf(__uint_as_float(v[i]));
+            if (i < p.head_ch) of[(int64_t)i * L] = tanh_fast(__uint_as_float(v[i]));
         }
       }
       if (up) {
@@ -718,7 +759,7 @@ cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t s
   auto kern = tc_stack_kernel<CP, KT, CS, TAIL>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
   if (e != cudaSuccess) return e;
-  return launch_pdl(kern, dim3(grid), dim3(64 + KT * CS * 128), smem, stream, p);
+  return launch_pdl(kern, dim3(grid), dim3(32 + 32 * ring_producers(CP) + KT * CS * 128), smem, stream, p);
 }
 
 }  // namespace
@@ -734,7 +775,7 @@ int tc_stack_kt(int cp) {
     case 96: return 2;
     case 64: return 3;
     case 48: return 2;
-    case 32: return 2;
+    case 32: return 3;
     default: return 0;
   }
 }
@@ -834,9 +875,9 @@ cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t
   TTSB_STACK_CASE(48, 2, 1, 0);
   TTSB_STACK_CASE(48, 2, 1, 1);
   TTSB_STACK_CASE(48, 2, 1, 2);
-  TTSB_STACK_CASE(32, 2, 1, 0);
-  TTSB_STACK_CASE(32, 2, 1, 1);
-  TTSB_STACK_CASE(32, 2, 1, 2);
+  TTSB_STACK_CASE(32, 3, 1, 0);
+  TTSB_STACK_CASE(32, 3, 1, 1);
+  TTSB_STACK_CASE(32, 3, 1, 2);
 #undef TTSB_STACK_CASE
   return cudaErrorInvalidConfiguration;
 }

@@ -217,6 +217,14 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// MUFU.TANH: relative error <= 2^-11, an order of magnitude below the BF16 operand rounding of this path
+// (tanhf is ~35 instructions per value; the head epilogue was 8 % of the last stage's instruction stream).
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // ---- LeakyReLU (0 <= slope <= 1, so lrelu(v) = max(v, slope v): no predicate chain) ----------------------
 __device__ __forceinline__ float lrelu_f(float v, float s) { return fmaxf(v, v * s); }
 // Packed bf16x2 form.  slope is split as s1 + s2 with s1 = bf16(slope), s2 = bf16(slope - s1), so that
