@@ -62,7 +62,7 @@ constexpr int ring_producers(int cp) { return cp > 96 ? 2 : 1; }
 struct Bars {
   uint64_t x_full[2], x_free[2];
   uint64_t w1_full[TC_STACK_MAX_BLOCKS], w2_full[TC_STACK_MAX_BLOCKS], w1_free, w2_free, wh_full;
-  uint64_t xa_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
+  uint64_t xa_ready[MAX_KT], xr_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
   uint64_t ring_full[RING_MAX_SLOTS], ring_empty[RING_MAX_SLOTS];
 };
 
@@ -84,6 +84,10 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
   // Ring mode (wide stages, one tile per CTA): a block's weights do not fit in shared memory, so they stream
   // through a ring of [RING_KB channels x CP columns] chunks in exactly the order the MMAs consume them.
   constexpr bool RING = CP > 96;
+  // Wide stages: epilogue 2 publishes lrelu(x) (what the next dilated conv needs) first and raw x + the D2 bias
+  // row afterwards behind a second barrier.  Narrow stages are instruction-issue bound; the extra barrier costs more
+  // than the shorter critical path gains (measured), so there everything is published at once.
+  constexpr bool SPLIT_E2 = CP >= 96;
   static_assert(!RING || KT == 1, "ring mode handles one tile per CTA");
   constexpr int NK = CP / RING_KB;                       // chunks per tap
   constexpr uint32_t SLOT_BYTES = RING_KB * CP * 2;
@@ -138,6 +142,7 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
     }
     for (int t = 0; t < KT; ++t) {
       mbar_init(&bars.xa_ready[t], GROUP_THREADS);
+      mbar_init(&bars.xr_ready[t], GROUP_THREADS);
       mbar_init(&bars.d1_full[t], 1);
       mbar_init(&bars.h_ready[t], GROUP_THREADS);
       mbar_init(&bars.d2_full[t], 1);
@@ -299,6 +304,7 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
             __syncwarp();
             // ---- 1x1 conv on h + 1x1 shortcut on raw x, both A operands in TMEM
             mbar_wait(&bars.h_ready[0], ph);
+            if (SPLIT_E2) mbar_wait(&bars.xr_ready[0], ph);
             tc_fence_after();
             for (int sx = 0; sx < 2; ++sx)
               for (int kc = 0; kc < NK; ++kc, ++gc) {
@@ -366,17 +372,21 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
           if (wsets == 1) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
           else if (it == 0) mbar_wait(&bars.w2_full[set], 0);
           tr(113);
-          if (leader) {
 #pragma unroll 1
-            for (int t = 0; t < KT; ++t) {
-              const uint32_t tcol = tbase + t * TCOLS;
+          for (int t = 0; t < KT; ++t) {
+            if (SPLIT_E2) {   // raw x and the D2 bias row: the off-critical-path half of epilogue 2
+              mbar_wait(&bars.xr_ready[t], ph);
+              tc_fence_after();
+            }
+            const uint32_t tcol = tbase + t * TCOLS;
+            if (leader) {
 #pragma unroll
               for (int kk = 0; kk < KS; ++kk)
                 umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
                              b_tmpl | (uint64_t)((w2 + CP * CP * 2 + 2 * kk * LBO_B) >> 4), idesc, 1);
             }
+            __syncwarp();
           }
-          __syncwarp();
 #pragma unroll 1
           for (int t = 0; t < KT; ++t) {
             mbar_wait(&bars.h_ready[t], ph);
@@ -551,16 +561,27 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
           const uint4 u = *reinterpret_cast<const uint4*>(src + (size_t)pl * plane_bytes);
           w[4 * pl] = u.x; w[4 * pl + 1] = u.y; w[4 * pl + 2] = u.z; w[4 * pl + 3] = u.w;
         }
-        tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+        // critical half first (what the dilated conv needs), then raw x and the D2 bias row for the 1x1 pair
         init_acc(tlane, s_bias[0][0]);
-        init_acc(tlane + CP, s_bias[0][1]);
+        if (!SPLIT_E2) {
+          tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+          init_acc(tlane + CP, s_bias[0][1]);
+        }
+        uint32_t a[CW / 2];
 #pragma unroll
-        for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
-        put_xa(w);
+        for (int i = 0; i < CW / 2; ++i) a[i] = lrelu_bf16x2(w[i], slope2);
+        put_xa(a);
         tmem_wait_st();
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(&bars.xa_ready[t]);
+        if (SPLIT_E2) {
+          tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+          init_acc(tlane + CP, s_bias[0][1]);
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(&bars.xr_ready[t]);
+        }
         tr(201);
       }
 
@@ -609,12 +630,11 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
           tr(223);
           uint32_t w[CW / 2];
           if (!last || tail) {
+            // Critical half: what the next MMA round needs — lrelu(x_new) in XA and its accumulator's bias row
+            // (the 1x1 MMAs of this tile have retired, so D1 | D2 are free).
             if (!last) {
-              // the 1x1 MMAs of this tile have retired: both accumulators may take the next block's biases
-              if (!DBG(16)) {
-                init_acc(tlane, s_bias[blk + 1][0]);
-                init_acc(tlane + CP, s_bias[blk + 1][1]);
-              }
+              if (!DBG(16)) init_acc(tlane, s_bias[blk + 1][0]);
+              if (!SPLIT_E2 && !DBG(16)) init_acc(tlane + CP, s_bias[blk + 1][1]);
             } else if (head) {
               uint32_t bv[16];
 #pragma unroll
@@ -630,14 +650,13 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
             }
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-            if (!last && !DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
-            if (!DBG(32)) {
+            if (!SPLIT_E2 && !last && !DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+            uint32_t a[CW / 2];
 #pragma unroll
-              for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
-            }
+            for (int i = 0; i < CW / 2; ++i) a[i] = DBG(32) ? w[i] : lrelu_bf16x2(w[i], slope2);
             tr(224);
-            if (last && up) put_xa_up(w);
-            else put_xa(w);
+            if (last && up) put_xa_up(a);
+            else put_xa(a);
             tr(225);
             tmem_wait_st();
             if (!DBG(8)) fence_proxy_async();
@@ -646,6 +665,15 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
             mbar_arrive(&bars.xa_ready[t]);
             tr(221);
             trw(321);
+            // Off the critical path: raw x (A operand of the shortcut) and the D2 bias row, needed only once the
+            // next dilated conv has been issued.
+            if (SPLIT_E2 && !last) {
+              if (!DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+              if (!DBG(16)) init_acc(tlane + CP, s_bias[blk + 1][1]);
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(&bars.xr_ready[t]);
+            }
           } else {
             const int tau = g0 + t * 128 + m;
             const bool own = tau >= chain * V && tau < (chain + 1) * V && tau < L;
