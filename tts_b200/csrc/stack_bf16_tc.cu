@@ -50,7 +50,9 @@ constexpr int MAX_KT = TC_STACK_MAX_KT;
 // 24 KB chunks from two warps = 90), so chunks are as large as the ring allows and two warps issue them.
 constexpr int RING_KB = 64;
 constexpr int RING_MAX_SLOTS = 12;
-constexpr int ring_producers(int cp) { return cp > 96 ? 2 : 1; }
+// Service warps after the epilogue groups: bulk-copy producer (+ TMEM owner), dilated-conv MMA issuer, and a third
+// warp that is the pointwise (1x1 pair + fused tail) MMA issuer, or in ring mode the second weight producer.
+constexpr int SERVICE_THREADS = 96;
 
 
 #ifdef TTSB_STACK_TRACE
@@ -69,9 +71,9 @@ struct Bars {
 // TAIL: what follows the last block — 0 the stack output is stored, 1 fused output head, 2 fused transposed conv
 // of the next stage.  A template parameter so each variant carries (and allocates registers for) its own code only.
 template <int CP, int KT, int CS, int TAIL>
-__global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ? 2 : 1)
+__global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ? 2 : 1)
     tc_stack_kernel(const __grid_constant__ TcStackParams p) {
-  constexpr int NT = 32 + 32 * ring_producers(CP) + KT * CS * 128;
+  constexpr int NT = SERVICE_THREADS + KT * CS * 128;
   constexpr int GROUP_THREADS = CS * 128;
   constexpr int PL = CP / 8;          // 8-channel planes
   constexpr int KS = CP / 16;         // K = 16 steps per tap
@@ -150,7 +152,7 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
     fence_mbar_init();
   }
   constexpr int PRODUCER_WARP = KT * CS * 4, MMA_WARP = PRODUCER_WARP + 1;
-  constexpr int PRODUCER2_WARP = MMA_WARP + 1;   // ring mode only: issues the odd weight chunks
+  constexpr int THIRD_WARP = MMA_WARP + 1;       // ring mode: issues the odd weight chunks; else: pointwise MMA issuer
   if (warp == PRODUCER_WARP) tmem_alloc(&tmem_base_s, TMEM_ALLOC);
   for (int e = tid; e < nb * 2 * CP; e += NT) {
     const int blk = e / (2 * CP), r = e - blk * 2 * CP;
@@ -235,7 +237,7 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
       }
       if (up_stream && n_w2 > 0) load_up(n_w2);   // tail weights of this CTA's last item
     }
-  } else if (RING && warp == PRODUCER2_WARP) {
+  } else if (RING && warp == THIRD_WARP) {
     // ================ second weight producer (ring mode): the odd chunks of the same sequence ================
     if (elect_one()) {
       for (int it = 0, gb = 0; blockIdx.x + it * gridDim.x < n_items; ++it)
@@ -251,225 +253,267 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
             bulk_g2s(sW + (size_t)slot * SLOT_BYTES, src, SLOT_BYTES, &bars.ring_full[slot]);
           }
     }
-  } else if (warp == MMA_WARP) {
-    // =============================== MMA issuer ===============================
+  } else if (RING && warp == MMA_WARP) {
+    // =============================== MMA issuer, ring mode ===============================
+    // One issuer: the weight chunks arrive through the ring in exactly the order the MMAs consume them.
     // The whole warp walks the loops (uniform control flow keeps addresses in uniform registers, so an MMA
     // costs a couple of uniform adds); only the tcgen05 instructions themselves are issued by the elected lane.
-    {
-      const bool leader = elect_one() != 0;
-      constexpr uint32_t idesc = make_idesc_bf16(128, CP);
-      constexpr uint32_t LBO_B = CP * 16;
-      const uint32_t lbo_a = plane_bytes;
-      // descriptor templates: only the 14-bit start-address field changes between MMAs
-      const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
-      Tracer tr = make_tracer(p.trace, 0, leader);
-      int gb = 0;
-      uint32_t n_xa = 0;   // completed xa_ready rounds (one per block, plus one per item with a fused tail conv)
-      uint32_t n_w2 = 0;   // consumed fills of the streamed W2S slot
-      for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
-        const int buf = it & 1;
-        const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
-        for (int blk = 0; blk < nb; ++blk, ++gb) {
-          const uint32_t ph = gb & 1;
-          const int set = wsets == 1 ? 0 : blk;
-          const uint32_t w1 = smem_u32(sW + (size_t)set * (W1_BYTES + W2_BYTES)), w2 = w1 + W1_BYTES;
-          const int d = p.dil[blk];
-          // ---- dilated conv: D1[t] = sum_tap XA[rows + (tap-1) d] W1[tap]^T
-          if (RING) {
-            mbar_wait(&bars.xa_ready[0], n_xa & 1);
+    const bool leader = elect_one() != 0;
+    constexpr uint32_t idesc = make_idesc_bf16(128, CP);
+    constexpr uint32_t LBO_B = CP * 16;
+    const uint32_t lbo_a = plane_bytes;
+    const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
+    int gb = 0;
+    for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
+      const int buf = it & 1;
+      const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
+      for (int blk = 0; blk < nb; ++blk, ++gb) {
+        const uint32_t ph = gb & 1;
+        const int d = p.dil[blk];
+        // ---- dilated conv: D1 = sum_tap XA[rows + (tap-1) d] W1[tap]^T
+        mbar_wait(&bars.xa_ready[0], ph);
+        tc_fence_after();
+        uint32_t gc = (uint32_t)gb * NCH;
+        for (int j = 0; j < TAPS; ++j) {
+          const uint32_t a_row = xa + (uint32_t)(G + (j - 1) * d) * 16;
+          for (int kc = 0; kc < NK; ++kc, ++gc) {
+            const int slot = gc % wsets;
+            mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
             tc_fence_after();
-            uint32_t gc = (uint32_t)gb * NCH;
-            for (int j = 0; j < TAPS; ++j) {
-              const uint32_t a_row = xa + (uint32_t)(G + (j - 1) * d) * 16;
-              for (int kc = 0; kc < NK; ++kc, ++gc) {
-                const int slot = gc % wsets;
-                mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
-                tc_fence_after();
-                if (leader) {
-                  const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
-#pragma unroll
-                  for (int kk = 0; kk < RING_KB / 16; ++kk)
-                    umma_bf16(tbase, a_tmpl | (uint64_t)((a_row + (uint32_t)(kc * (RING_KB / 8) + 2 * kk) * lbo_a) >> 4),
-                              b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
-                  umma_commit(&bars.ring_empty[slot]);
-                }
-                __syncwarp();
-              }
-            }
-            ++n_xa;
             if (leader) {
-              umma_commit(&bars.d1_full[0]);
-              if (blk == nb - 1 && !tail) umma_commit(&bars.x_free[buf]);
+              const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
+#pragma unroll
+              for (int kk = 0; kk < RING_KB / 16; ++kk)
+                umma_bf16(tbase, a_tmpl | (uint64_t)((a_row + (uint32_t)(kc * (RING_KB / 8) + 2 * kk) * lbo_a) >> 4),
+                          b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
+              umma_commit(&bars.ring_empty[slot]);
             }
             __syncwarp();
-            // ---- 1x1 conv on h + 1x1 shortcut on raw x, both A operands in TMEM
-            mbar_wait(&bars.h_ready[0], ph);
-            if (SPLIT_E2) mbar_wait(&bars.xr_ready[0], ph);
-            tc_fence_after();
-            for (int sx = 0; sx < 2; ++sx)
-              for (int kc = 0; kc < NK; ++kc, ++gc) {
-                const int slot = gc % wsets;
-                mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
-                tc_fence_after();
-                if (leader) {
-                  const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
-                  const uint32_t acol = tbase + (sx ? 2 * CP : 0) + 8 * (kc * (RING_KB / 16));
-#pragma unroll
-                  for (int kk = 0; kk < RING_KB / 16; ++kk)
-                    umma_bf16_ts(tbase + CP, acol + 8 * kk, b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
-                  umma_commit(&bars.ring_empty[slot]);
-                }
-                __syncwarp();
-              }
-            if (leader) umma_commit(&bars.d2_full[0]);
-            __syncwarp();
-            continue;
           }
-          if (wsets == 1) mbar_wait(&bars.w1_full[0], ph);
-          else if (it == 0) mbar_wait(&bars.w1_full[set], 0);
-          // Issue order: tap j of tile t reads rows shifted by (j - 1) d, so taps 0 and 1 need tiles <= t only and
-          // start as soon as tile t has been rewritten; tap 2 follows once tile t + 1 is there.  The last tile's
-          // epilogue 2 thereby overlaps the first two taps of the tiles before it.
-          auto issue_taps = [&](int t, int j0, int j1) {
-            const uint32_t dcol = tbase + t * TCOLS;
+        }
+        if (leader) {
+          umma_commit(&bars.d1_full[0]);
+          if (blk == nb - 1) umma_commit(&bars.x_free[buf]);
+        }
+        __syncwarp();
+        // ---- 1x1 conv on h + 1x1 shortcut on raw x, both A operands in TMEM
+        mbar_wait(&bars.h_ready[0], ph);
+        if (SPLIT_E2) mbar_wait(&bars.xr_ready[0], ph);
+        tc_fence_after();
+        for (int sx = 0; sx < 2; ++sx)
+          for (int kc = 0; kc < NK; ++kc, ++gc) {
+            const int slot = gc % wsets;
+            mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
+            tc_fence_after();
             if (leader) {
+              const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
+              const uint32_t acol = tbase + (sx ? 2 * CP : 0) + 8 * (kc * (RING_KB / 16));
 #pragma unroll
-              for (int j = j0; j < j1; ++j) {
-                const uint32_t a_row = xa + (uint32_t)(G + t * 128 + (j - 1) * d) * 16;
-                const uint32_t w_tap = w1 + (uint32_t)j * (CP * CP * 2);
-#pragma unroll
-                for (int kk = 0; kk < KS; ++kk)
-                  umma_bf16(dcol, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
-                            b_tmpl | (uint64_t)((w_tap + 2 * kk * LBO_B) >> 4), idesc, 1);
-              }
+              for (int kk = 0; kk < RING_KB / 16; ++kk)
+                umma_bf16_ts(tbase + CP, acol + 8 * kk, b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
+              umma_commit(&bars.ring_empty[slot]);
             }
-          };
-#pragma unroll 1
-          for (int t = 0; t < KT; ++t) {
-            mbar_wait(&bars.xa_ready[t], n_xa & 1);
-            tc_fence_after();
-            tr(100 + t);
-            if (t > 0) {
-              issue_taps(t - 1, 2, 3);
-              if (leader) umma_commit(&bars.d1_full[t - 1]);
-            }
-            issue_taps(t, 0, 2);
             __syncwarp();
-            tr(110 + t);
           }
-          issue_taps(KT - 1, 2, 3);
-          if (leader) umma_commit(&bars.d1_full[KT - 1]);
-          __syncwarp();
-          ++n_xa;
+        if (leader) umma_commit(&bars.d2_full[0]);
+        __syncwarp();
+      }
+    }
+  } else if (!RING && warp == MMA_WARP) {
+    // =============================== conv issuer: the dilated convs ===============================
+    // Two issuing warps, so that a tile's 1x1 pair (and the fused tail) never queues behind the barrier waits of
+    // the other tiles' dilated convs and vice versa: this warp follows xa_ready, the pointwise issuer follows
+    // h_ready / xr_ready.  All cross-warp ordering is carried by mbarriers (tcgen05.commit tracks the MMAs of
+    // the committing thread only, and each barrier is committed by the warp that issued what it guards).
+    // The whole warp walks the loops (uniform control flow keeps addresses in uniform registers, so an MMA
+    // costs a couple of uniform adds); only the tcgen05 instructions themselves are issued by the elected lane.
+    // (Measured alternatives that lost: polling all tiles' barriers with one ballot of test_waits and issuing
+    // whatever is ready — the polls cost more than the in-order waits; one CTA per SM with 5-6 tiles — this
+    // warp's issue rate, ~120 cycles per MMA at N = 32, then bounds the stage.)
+    const bool leader = elect_one() != 0;
+    constexpr uint32_t idesc = make_idesc_bf16(128, CP);
+    constexpr uint32_t LBO_B = CP * 16;
+    const uint32_t lbo_a = plane_bytes;
+    // descriptor templates: only the 14-bit start-address field changes between MMAs
+    const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
+    Tracer tr = make_tracer(p.trace, 0, leader);
+    int gb = 0;
+    uint32_t n_xa = 0;   // completed xa_ready rounds (one per block, plus one per item with a fused tail conv)
+    for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
+      const int buf = it & 1;
+      const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
+      for (int blk = 0; blk < nb; ++blk, ++gb) {
+        const int set = wsets == 1 ? 0 : blk;
+        const uint32_t w1 = smem_u32(sW + (size_t)set * (W1_BYTES + W2_BYTES));
+        const int d = p.dil[blk];
+        if (wsets == 1) mbar_wait(&bars.w1_full[0], gb & 1);
+        else if (it == 0) mbar_wait(&bars.w1_full[set], 0);
+        // Issue order: tap j of tile t reads rows shifted by (j - 1) d, so taps 0 and 1 need tiles <= t only and
+        // start as soon as tile t has been rewritten; tap 2 follows once tile t + 1 is there.
+        auto issue_taps = [&](int t, int j0, int j1) {
+          const uint32_t dcol = tbase + t * TCOLS;
           if (leader) {
-            if (wsets == 1) umma_commit(&bars.w1_free);
-            if (blk == nb - 1 && !tail) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
-          }
-          __syncwarp();
-          tr(112);
-          // ---- D2[t] = S x (raw x in TMEM: ready since the previous round's epilogue 2, so these fill the wait for
-          // epilogue 1) + W2 h (h in TMEM, written by epilogue 1)
-          if (wsets == 1) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
-          else if (it == 0) mbar_wait(&bars.w2_full[set], 0);
-          tr(113);
-#pragma unroll 1
-          for (int t = 0; t < KT; ++t) {
-            if (SPLIT_E2) {   // raw x and the D2 bias row: the off-critical-path half of epilogue 2
-              mbar_wait(&bars.xr_ready[t], ph);
-              tc_fence_after();
-            }
-            const uint32_t tcol = tbase + t * TCOLS;
-            if (leader) {
+#pragma unroll
+            for (int j = j0; j < j1; ++j) {
+              const uint32_t a_row = xa + (uint32_t)(G + t * 128 + (j - 1) * d) * 16;
+              const uint32_t w_tap = w1 + (uint32_t)j * (CP * CP * 2);
 #pragma unroll
               for (int kk = 0; kk < KS; ++kk)
-                umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
-                             b_tmpl | (uint64_t)((w2 + CP * CP * 2 + 2 * kk * LBO_B) >> 4), idesc, 1);
+                umma_bf16(dcol, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
+                          b_tmpl | (uint64_t)((w_tap + 2 * kk * LBO_B) >> 4), idesc, 1);
             }
-            __syncwarp();
           }
+        };
 #pragma unroll 1
-          for (int t = 0; t < KT; ++t) {
-            mbar_wait(&bars.h_ready[t], ph);
-            tr(116 + t);
-            tc_fence_after();
-            tr(120 + t);
-            const uint32_t tcol = tbase + t * TCOLS;
-            if (leader) {
+        for (int t = 0; t < KT; ++t) {
+          mbar_wait(&bars.xa_ready[t], n_xa & 1);
+          tc_fence_after();
+          tr(100 + t);
+          if (t > 0) {
+            issue_taps(t - 1, 2, 3);
+            if (leader) umma_commit(&bars.d1_full[t - 1]);
+          }
+          issue_taps(t, 0, 2);
+          __syncwarp();
+          tr(110 + t);
+        }
+        issue_taps(KT - 1, 2, 3);
+        if (leader) {
+          umma_commit(&bars.d1_full[KT - 1]);
+          if (wsets == 1) umma_commit(&bars.w1_free);
+          if (blk == nb - 1 && !tail) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
+        }
+        __syncwarp();
+        ++n_xa;
+        tr(112);
+      }
+      if (tail) {
+        // The tail round of xa_ready belongs to the pointwise issuer; pass it here too so that this warp's
+        // parity never runs a full phase ahead of the barrier (a parity wait cannot tell phase n from n + 2).
+#pragma unroll 1
+        for (int t = 0; t < KT; ++t) mbar_wait(&bars.xa_ready[t], n_xa & 1);
+        ++n_xa;
+      }
+    }
+  } else if (!RING && warp == THIRD_WARP) {
+    // =============================== pointwise issuer: 1x1 pair, fused tail ===============================
+    const bool leader = elect_one() != 0;
+    constexpr uint32_t idesc = make_idesc_bf16(128, CP);
+    constexpr uint32_t LBO_B = CP * 16;
+    const uint32_t lbo_a = plane_bytes;
+    const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
+    Tracer tr = make_tracer(p.trace, TRACE_ROLES - 1, leader);
+    int gb = 0;
+    uint32_t n_xa = 0;   // same count as the conv issuer's
+    uint32_t n_w2 = 0;   // consumed fills of the streamed W2S slot
+    for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
+      const int buf = it & 1;
+      const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
+      for (int blk = 0; blk < nb; ++blk, ++gb) {
+        const uint32_t ph = gb & 1;
+        const int set = wsets == 1 ? 0 : blk;
+        const uint32_t w2 = smem_u32(sW + (size_t)set * (W1_BYTES + W2_BYTES)) + W1_BYTES;
+        if (wsets == 1) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
+        else if (it == 0) mbar_wait(&bars.w2_full[set], 0);
+        tr(113);
+        // ---- D2[t] = S x (raw x in TMEM since the previous round's epilogue 2: these run while epilogue 1 works)
+#pragma unroll 1
+        for (int t = 0; t < KT; ++t) {
+          if (SPLIT_E2) mbar_wait(&bars.xr_ready[t], ph);      // raw x + D2 bias row: the deferred half of epilogue 2
+          else mbar_wait(&bars.xa_ready[t], n_xa & 1);         // published together with lrelu(x)
+          tc_fence_after();
+          const uint32_t tcol = tbase + t * TCOLS;
+          if (leader) {
+#pragma unroll
+            for (int kk = 0; kk < KS; ++kk)
+              umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
+                           b_tmpl | (uint64_t)((w2 + CP * CP * 2 + 2 * kk * LBO_B) >> 4), idesc, 1);
+          }
+          __syncwarp();
+        }
+        ++n_xa;
+        // ---- ... + W2 h (h in TMEM, written by epilogue 1)
+#pragma unroll 1
+        for (int t = 0; t < KT; ++t) {
+          mbar_wait(&bars.h_ready[t], ph);
+          tc_fence_after();
+          tr(120 + t);
+          const uint32_t tcol = tbase + t * TCOLS;
+          if (leader) {
+#pragma unroll
+            for (int kk = 0; kk < KS; ++kk)
+              umma_bf16_ts(tcol + CP, tcol + 8 * kk, b_tmpl | (uint64_t)((w2 + 2 * kk * LBO_B) >> 4), idesc, 1);
+            umma_commit(&bars.d2_full[t]);
+          }
+          __syncwarp();
+          tr(130 + t);
+        }
+        if (leader && wsets == 1) umma_commit(&bars.w2_free);
+        __syncwarp();
+      }
+      if (head) {
+        // ---- fused output head: D1[t][0:16] = sum_tap lrelu(x_out)[rows + tap - hh] Wh[tap]^T   (N = 16)
+        constexpr uint32_t idesc_h = make_idesc_bf16(128, 16);
+        const uint64_t bh_tmpl = make_desc(0, 16 * 16, 128);
+        const uint32_t wh = smem_u32(sWH);
+        if (it == 0) mbar_wait(&bars.wh_full, 0);
+#pragma unroll 1
+        for (int t = 0; t < KT; ++t) {
+          if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
+          if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
+          tc_fence_after();
+          if (leader) {
+            for (int j = 0; j < p.head_taps; ++j) {
+              const uint32_t a_row = xa + (uint32_t)(G + t * 128 + j - hh) * 16;
+              const uint32_t w_tap = wh + (uint32_t)j * (CP * 16 * 2);
 #pragma unroll
               for (int kk = 0; kk < KS; ++kk)
-                umma_bf16_ts(tcol + CP, tcol + 8 * kk, b_tmpl | (uint64_t)((w2 + 2 * kk * LBO_B) >> 4), idesc, 1);
-              umma_commit(&bars.d2_full[t]);
+                umma_bf16(tbase + t * TCOLS, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
+                          bh_tmpl | (uint64_t)((w_tap + 2 * kk * 256) >> 4), idesc_h, 1);
             }
-            __syncwarp();
-            tr(130 + t);
+            umma_commit(&bars.d1_full[t]);
           }
-          if (leader && wsets == 1) umma_commit(&bars.w2_free);
           __syncwarp();
         }
-        if (head) {
-          // ---- fused output head: D1[t][0:16] = sum_tap lrelu(x_out)[rows + tap - hh] Wh[tap]^T   (N = 16)
-          constexpr uint32_t idesc_h = make_idesc_bf16(128, 16);
-          const uint64_t bh_tmpl = make_desc(0, 16 * 16, 128);
-          const uint32_t wh = smem_u32(sWH);
-          if (it == 0) mbar_wait(&bars.wh_full, 0);
+        ++n_xa;
+        if (leader) umma_commit(&bars.x_free[buf]);
+        __syncwarp();
+      }
+      if (up) {
+        // ---- fused transposed conv of the next stage: D[t][0:N] = a[q] Wu[0]^T + a[q-1] Wu[1]^T, a = lrelu(x_out)
+        const int N = p.up_n;
+        const uint32_t idesc_u = make_idesc_bf16(128, N);
+        const uint32_t lbo_u = (uint32_t)N * 16;
+        const uint64_t bu_tmpl = make_desc(0, lbo_u, 128);
+        const bool resident = p.up_mode == 1;
+        const uint32_t wu = smem_u32(resident ? sWH : sW + W1_BYTES);
+        if (!resident) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
+        else if (it == 0) mbar_wait(&bars.wh_full, 0);
 #pragma unroll 1
-          for (int t = 0; t < KT; ++t) {
-            if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
-            if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
-            tc_fence_after();
-            if (leader) {
-              for (int j = 0; j < p.head_taps; ++j) {
-                const uint32_t a_row = xa + (uint32_t)(G + t * 128 + j - hh) * 16;
-                const uint32_t w_tap = wh + (uint32_t)j * (CP * 16 * 2);
-#pragma unroll
-                for (int kk = 0; kk < KS; ++kk)
-                  umma_bf16(tbase + t * TCOLS, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
-                            bh_tmpl | (uint64_t)((w_tap + 2 * kk * 256) >> 4), idesc_h, 1);
-              }
-              umma_commit(&bars.d1_full[t]);
-            }
-            __syncwarp();
-          }
-          ++n_xa;
-          if (leader) umma_commit(&bars.x_free[buf]);
-          __syncwarp();
-        }
-        if (up) {
-          // ---- fused transposed conv of the next stage: D[t][0:N] = a[q] Wu[0]^T + a[q-1] Wu[1]^T, a = lrelu(x_out)
-          const int N = p.up_n;
-          const uint32_t idesc_u = make_idesc_bf16(128, N);
-          const uint32_t lbo_u = (uint32_t)N * 16;
-          const uint64_t bu_tmpl = make_desc(0, lbo_u, 128);
-          const bool resident = p.up_mode == 1;
-          const uint32_t wu = smem_u32(resident ? sWH : sW + W1_BYTES);
-          if (!resident) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
-          else if (it == 0) mbar_wait(&bars.wh_full, 0);
-#pragma unroll 1
-          for (int t = 0; t < KT; ++t) {
-            mbar_wait(&bars.xa_ready[t], n_xa & 1);   // taps reach back one row only: tile t needs tiles <= t
-            tc_fence_after();
-            tr(140 + t);
-            if (leader) {
-#pragma unroll
-              for (int j = 0; j < 2; ++j) {
-                const uint32_t a_row = xa + (uint32_t)(G + t * 128 - j) * 16;
-                const uint32_t w_tap = wu + (uint32_t)j * (uint32_t)(CP * N * 2);
-#pragma unroll
-                for (int kk = 0; kk < KS; ++kk)
-                  umma_bf16(tbase + t * TCOLS, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
-                            bu_tmpl | (uint64_t)((w_tap + 2 * kk * lbo_u) >> 4), idesc_u, 1);
-              }
-              umma_commit(&bars.d1_full[t]);
-            }
-            __syncwarp();
-          }
-          ++n_xa;
+        for (int t = 0; t < KT; ++t) {
+          mbar_wait(&bars.xa_ready[t], n_xa & 1);   // taps reach back one row only: tile t needs tiles <= t
+          tc_fence_after();
+          tr(140 + t);
           if (leader) {
-            if (!resident) umma_commit(&bars.w2_free);
-            umma_commit(&bars.x_free[buf]);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const uint32_t a_row = xa + (uint32_t)(G + t * 128 - j) * 16;
+              const uint32_t w_tap = wu + (uint32_t)j * (uint32_t)(CP * N * 2);
+#pragma unroll
+              for (int kk = 0; kk < KS; ++kk)
+                umma_bf16(tbase + t * TCOLS, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
+                          bu_tmpl | (uint64_t)((w_tap + 2 * kk * lbo_u) >> 4), idesc_u, 1);
+            }
+            umma_commit(&bars.d1_full[t]);
           }
           __syncwarp();
         }
+        ++n_xa;
+        if (leader) {
+          if (!resident) umma_commit(&bars.w2_free);
+          umma_commit(&bars.x_free[buf]);
+        }
+        __syncwarp();
       }
     }
   } else {
@@ -484,8 +528,9 @@ __global__ void __launch_bounds__(32 + 32 * ring_producers(CP) + KT * CS * 128, 
     const Slope2 slope2 = make_slope2(slope);
     const int L = p.L;
     const int pair_bar = 1 + t * 4 + q4;        // named barrier shared by the CS warps of a quarter
-    Tracer tr = make_tracer(p.trace, 1 + t, m == 0 && cs == 0);
-    Tracer trw = make_tracer(p.trace, 1 + KT + warp, lane == 0);   // per-warp arrival times
+    // debug bit 512: issuer timelines only (the epilogue trace points perturb the kernel by ~20 %)
+    Tracer tr = make_tracer(p.trace, 1 + t, m == 0 && cs == 0 && !DBG(512));
+    Tracer trw = make_tracer(p.trace, 1 + KT + warp, lane == 0 && !DBG(512));   // per-warp arrival times
     uint32_t n_d1 = 0;                          // completed d1_full rounds (blocks, plus the fused head)
 
     int gb = 0;
@@ -787,7 +832,7 @@ cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t s
   auto kern = tc_stack_kernel<CP, KT, CS, TAIL>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
   if (e != cudaSuccess) return e;
-  return launch_pdl(kern, dim3(grid), dim3(32 + 32 * ring_producers(CP) + KT * CS * 128), smem, stream, p);
+  return launch_pdl(kern, dim3(grid), dim3(SERVICE_THREADS + KT * CS * 128), smem, stream, p);
 }
 
 }  // namespace
@@ -796,16 +841,31 @@ int tc_stack_ctas_per_sm(int cp) { return tc_stack_kt(cp) * 5 * cp / 2 <= 256 ? 
 
 int tc_stack_cs(int cp) { return cp >= 128 ? 4 : cp == 96 ? 2 : 1; }
 
+// 128-row tiles per work item.  Narrow stages (cp <= 48) run two CTAs per SM with half the TMEM each; one CTA per
+// SM with twice the tiles measured slower (cp = 32: KT 6 -> 0.099 ms vs KT 3 x 2 CTAs -> 0.087 ms): a single conv
+// issuer then has to feed every tile.  TTSB200_STACK_KT_<cp>=<kt> overrides the choice for experiments (the value
+// must have an instantiation in dispatch()).
 int tc_stack_kt(int cp) {
+  static int cache[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};   // cp -> kt, filled on first use per cp
+  int dflt;
   switch (cp) {
     case 192: return 1;
     case 128: return 1;
     case 96: return 2;
     case 64: return 3;
-    case 48: return 2;
-    case 32: return 3;
+    case 48: dflt = 2; break;
+    case 32: dflt = 3; break;
     default: return 0;
   }
+  const int slot = cp == 48 ? 0 : 1;
+  if (cache[slot][0] != cp) {
+    char name[32];
+    snprintf(name, sizeof name, "TTSB200_STACK_KT_%d", cp);
+    const char* e = getenv(name);
+    cache[slot][1] = e ? atoi(e) : dflt;
+    cache[slot][0] = cp;
+  }
+  return cache[slot][1];
 }
 
 // Fills kt / guard / w_sets for a stage (cp, dilations, nblocks set by the caller); returns false when the
@@ -850,9 +910,12 @@ bool tc_stack_configure(TcStackParams& p) {
   }
   if (xa + wset + wh > budget) return false;
   p.w_sets = (!up && xa + p.nblocks * wset + wh <= budget) ? p.nblocks : 1;
-  if (up) {   // tail weights: resident beside the streamed block weights when they fit, else sharing the W2S slot
+  if (up) {   // tail weights: resident beside the block weights when they fit, else sharing the streamed W2S slot
     const size_t wu = (size_t)2 * p.cp * p.up_n * 2;
-    if (xa + wset + wu <= budget) p.up_mode = 1;
+    if (xa + p.nblocks * wset + wu <= budget) {
+      p.w_sets = p.nblocks;
+      p.up_mode = 1;
+    } else if (xa + wset + wu <= budget) p.up_mode = 1;
     else if (p.up_n <= p.cp) p.up_mode = 2;
     else return false;
   }
@@ -892,7 +955,7 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
 cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
   const int tail = p.head_w ? 1 : p.up_w ? 2 : 0;
 #define TTSB_STACK_CASE(CP, KT, CS, TAIL) \
-  if (p.cp == CP && tail == TAIL) return launch<CP, KT, CS, TAIL>(p, smem, grid, stream)
+  if (p.cp == CP && p.kt == KT && tail == TAIL) return launch<CP, KT, CS, TAIL>(p, smem, grid, stream)
   TTSB_STACK_CASE(192, 1, 4, 0);
   TTSB_STACK_CASE(128, 1, 4, 0);
   TTSB_STACK_CASE(96, 2, 2, 0);
@@ -900,12 +963,20 @@ cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t
   TTSB_STACK_CASE(64, 3, 1, 0);
   TTSB_STACK_CASE(64, 3, 1, 1);
   TTSB_STACK_CASE(64, 3, 1, 2);
+  TTSB_STACK_CASE(48, 4, 1, 0);
+  TTSB_STACK_CASE(48, 4, 1, 1);
+  TTSB_STACK_CASE(48, 4, 1, 2);
+  TTSB_STACK_CASE(32, 6, 1, 0);
+  TTSB_STACK_CASE(32, 6, 1, 1);
+  TTSB_STACK_CASE(32, 6, 1, 2);
+  // experiment variants (TTSB200_STACK_KT_<cp>)
   TTSB_STACK_CASE(48, 2, 1, 0);
   TTSB_STACK_CASE(48, 2, 1, 1);
   TTSB_STACK_CASE(48, 2, 1, 2);
   TTSB_STACK_CASE(32, 3, 1, 0);
   TTSB_STACK_CASE(32, 3, 1, 1);
   TTSB_STACK_CASE(32, 3, 1, 2);
+  TTSB_STACK_CASE(32, 5, 1, 1);
 #undef TTSB_STACK_CASE
   return cudaErrorInvalidConfiguration;
 }

@@ -75,7 +75,7 @@ struct TcCanonOut {
 // Fused ResidualStack (melgan.py:36-39): x <- S_b x + W2_b lrelu(W1_b * lrelu(x)) for b = 0..n-1 in ONE
 // persistent kernel: lrelu(x) in shared memory, raw x / h / accumulators in TMEM (stack_bf16_tc.cu).
 constexpr int TC_STACK_MAX_BLOCKS = 4;
-constexpr int TC_STACK_MAX_KT = 4;
+constexpr int TC_STACK_MAX_KT = 6;
 struct TcStackParams {
   const __nv_bfloat16* x;  // canonical raw input (no margins needed)
   int64_t x_batch_stride;

@@ -32,7 +32,7 @@ struct Tracer {
 __device__ __forceinline__ Tracer make_tracer(long long*, int, bool) { return Tracer{}; }
 #endif
 
-constexpr int TRACE_ROLES = 24;
+constexpr int TRACE_ROLES = 40;
 
 // Host side: allocate before the launch, dump + free after it.
 inline long long* trace_begin(cudaStream_t stream) {
