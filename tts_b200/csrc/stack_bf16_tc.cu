@@ -90,6 +90,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   // row afterwards behind a second barrier.  Narrow stages are instruction-issue bound; the extra barrier costs more
   // than the shorter critical path gains (measured), so there everything is published at once.
   constexpr bool SPLIT_E2 = CP >= 96;
+  // ... and run epilogue 2 in 16-column chunks (see there); narrow stages do it all at once.
+  constexpr bool CHUNKED_E2 = CP >= 96;
   static_assert(!RING || KT == 1, "ring mode handles one tile per CTA");
   constexpr int NK = CP / RING_KB;                       // chunks per tap
   constexpr uint32_t SLOT_BYTES = RING_KB * CP * 2;
@@ -595,6 +597,67 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         tmem_st<CW>(taddr + c0, bv);
       };
 
+      // Where this thread's row goes in XA for the whole item (byte offsets within a plane, -1 = nowhere): its own
+      // staged row, the mirror rows ReflectionPad1d reads near a sequence end, and for the fused transposed conv
+      // the zero rows either side of the sequence.  Computed once per item: epilogue 2 stores chunk by chunk.
+      int o_main = (G + t * 128 + m) * 16, o_mlo = -1, o_mhi = -1, o_zlo = -1, o_zhi = -1;
+      if (edge) {
+        const int tau = g0 + t * 128 + m;
+        if (tau < 0 || tau >= L) o_main = -1;
+        else {
+          if (tau >= 1 && tau <= G && -tau - g0 >= -G) o_mlo = (G - tau - g0) * 16;
+          const int back = L - 1 - tau;
+          if (back >= 1 && back <= G && L - 1 + back - g0 < TR + G) o_mhi = (G + L - 1 + back - g0) * 16;
+          if (tau == 0) o_zlo = (G - 1 - g0) * 16;
+          if (tau == L - 1) o_zhi = (G + L - g0) * 16;
+        }
+      }
+      // 16 channels (two planes) of this thread's row -> XA.  `zero_pad`: the round feeds the fused transposed conv
+      auto xa_store16 = [&](int c, const uint32_t* a8, bool zero_pad) {
+        uint8_t* base = xa + (size_t)(c / 8) * plane_bytes;
+        const uint4 lo = make_uint4(a8[0], a8[1], a8[2], a8[3]), hi = make_uint4(a8[4], a8[5], a8[6], a8[7]);
+        if (!edge) {
+          *reinterpret_cast<uint4*>(base + o_main) = lo;
+          *reinterpret_cast<uint4*>(base + plane_bytes + o_main) = hi;
+          return;
+        }
+        if (o_main < 0) return;
+        *reinterpret_cast<uint4*>(base + o_main) = lo;
+        *reinterpret_cast<uint4*>(base + plane_bytes + o_main) = hi;
+        if (!zero_pad) {
+          if (o_mlo >= 0) {
+            *reinterpret_cast<uint4*>(base + o_mlo) = lo;
+            *reinterpret_cast<uint4*>(base + plane_bytes + o_mlo) = hi;
+          }
+          if (o_mhi >= 0) {
+            *reinterpret_cast<uint4*>(base + o_mhi) = lo;
+            *reinterpret_cast<uint4*>(base + plane_bytes + o_mhi) = hi;
+          }
+        } else {
+          const uint4 z = make_uint4(0, 0, 0, 0);
+          if (o_zlo >= 0) {
+            *reinterpret_cast<uint4*>(base + o_zlo) = z;
+            *reinterpret_cast<uint4*>(base + plane_bytes + o_zlo) = z;
+          }
+          if (o_zhi >= 0) {
+            *reinterpret_cast<uint4*>(base + o_zhi) = z;
+            *reinterpret_cast<uint4*>(base + plane_bytes + o_zhi) = z;
+          }
+        }
+      };
+      // 16 accumulator columns <- their bias values
+      auto init_acc16 = [&](uint32_t taddr, const float* bias_row, int c) {
+        uint32_t bv[16];
+        const float4* src = reinterpret_cast<const float4*>(bias_row + c0 + c);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 f = src[i];
+          bv[4 * i] = __float_as_uint(f.x); bv[4 * i + 1] = __float_as_uint(f.y);
+          bv[4 * i + 2] = __float_as_uint(f.z); bv[4 * i + 3] = __float_as_uint(f.w);
+        }
+        tmem_st<16>(taddr + c0 + c, bv);
+      };
+
       // ---- prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place; accumulators <- block 0 biases
       mbar_wait_relaxed(&bars.x_full[buf], (it >> 1) & 1);
       tr(200);
@@ -669,14 +732,66 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           tc_fence_after();
           tr(220);
           trw(320);
-          uint32_t v[CW];
-          tmem_ld_nw<CW>(tlane + CP + c0, v);
-          tmem_wait_ld();
-          tr(223);
-          uint32_t w[CW / 2];
-          if (!last || tail) {
-            // Critical half: what the next MMA round needs — lrelu(x_new) in XA and its accumulator's bias row
-            // (the 1x1 MMAs of this tile have retired, so D1 | D2 are free).
+          if (CHUNKED_E2 && (!last || tail)) {
+            // What the next MMA round needs: lrelu(x_new) in XA, raw x_new in XR[t] and the accumulators' bias rows
+            // (the 1x1 MMAs of this tile have retired, so D1 | D2 are free).  Done in chunks of 16 columns — load,
+            // convert, store, with the next chunk's TMEM load in flight — so that the live set stays ~50 registers
+            // (the all-at-once form held 2 * CW values and spilled in this loop) and the first stores start early.
+            static_assert(CW % 16 == 0, "epilogue 2 works in 16-column chunks");
+            uint32_t v[2][16];
+            tmem_ld16_nw(tlane + CP + c0, v[0]);
+#pragma unroll
+            for (int c = 0; c < CW; c += 16) {
+              uint32_t* vc = v[(c / 16) & 1];
+              tmem_wait_ld();
+              if (c + 16 < CW) tmem_ld16_nw(tlane + CP + c0 + c + 16, v[((c / 16) & 1) ^ 1]);
+              uint32_t w8[8], a8[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) w8[i] = pack_bf16x2(__uint_as_float(vc[2 * i]), __uint_as_float(vc[2 * i + 1]));
+#pragma unroll
+              for (int i = 0; i < 8; ++i) a8[i] = lrelu_bf16x2(w8[i], slope2);
+              xa_store16(c, a8, last && up);
+              if (!last) {
+                tmem_st8(tlane + 2 * CP + (c0 + c) / 2, w8);
+                init_acc16(tlane, s_bias[blk + 1][0], c);
+                if (!SPLIT_E2) init_acc16(tlane + CP, s_bias[blk + 1][1], c);
+              }
+            }
+            if (last && head) {
+              uint32_t bv[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_head[i]);
+              tmem_st<16>(tlane, bv);            // head accumulator <- head bias
+            } else if (last) {
+              for (int c = cs * UW; c < (cs + 1) * UW; c += 16) {   // transposed-conv accumulator <- its bias
+                uint32_t bv[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_up[c + i]);
+                tmem_st<16>(tlane + c, bv);
+              }
+            }
+            tr(225);
+            tmem_wait_st();
+            fence_proxy_async();
+            tr(226);
+            tc_fence_before();
+            mbar_arrive(&bars.xa_ready[t]);
+            tr(221);
+            trw(321);
+            // Off the critical path: the D2 bias row, needed only by the 1x1 pair after the next dilated conv.
+            if (SPLIT_E2 && !last) {
+              init_acc(tlane + CP, s_bias[blk + 1][1]);
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(&bars.xr_ready[t]);
+            }
+          } else if (!last || tail) {
+            // Narrow stages (two CTAs per SM, instruction-issue bound): everything at once — one TMEM load and one
+            // wait; the chunked form's extra waits cost more than its shorter live ranges gain (measured: +10 % at 48).
+            uint32_t v[CW], w[CW / 2];
+            tmem_ld_nw<CW>(tlane + CP + c0, v);
+            tmem_wait_ld();
+            tr(223);
             if (!last) {
               if (!DBG(16)) init_acc(tlane, s_bias[blk + 1][0]);
               if (!SPLIT_E2 && !DBG(16)) init_acc(tlane + CP, s_bias[blk + 1][1]);
@@ -710,8 +825,6 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             mbar_arrive(&bars.xa_ready[t]);
             tr(221);
             trw(321);
-            // Off the critical path: raw x (A operand of the shortcut) and the D2 bias row, needed only once the
-            // next dilated conv has been issued.
             if (SPLIT_E2 && !last) {
               if (!DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
               if (!DBG(16)) init_acc(tlane + CP, s_bias[blk + 1][1]);
@@ -720,6 +833,9 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
               mbar_arrive(&bars.xr_ready[t]);
             }
           } else {
+            uint32_t v[CW], w[CW / 2];
+            tmem_ld_nw<CW>(tlane + CP + c0, v);
+            tmem_wait_ld();
             const int tau = g0 + t * 128 + m;
             const bool own = tau >= chain * V && tau < (chain + 1) * V && tau < L;
             if (own) {
