@@ -112,7 +112,9 @@ def test_forward_equals_inference_without_padding():
     sub = m(mel)                                            # eval forward: sub-bands, no PQMF
     assert sub.shape == (2, 4, 20 * 64)
     full = m.inference(mel)
-    assert torch.equal(m.pqmf_synthesis(sub), full)
+    # the generator runs the factorised synthesis (24 MACs/sample), the stand-alone op the direct 63-tap form:
+    # same sums in a different association, so fp32 rounding apart
+    assert float((m.pqmf_synthesis(sub) - full).abs().max()) <= 2e-6
 
 
 def test_too_short_input_raises_like_reference():

@@ -67,6 +67,8 @@ struct ttsb200_plan {
   int halo = 8;                     // margin rows either side of every canonical activation plane
   std::vector<ttsb::StagePlan> stages;
   size_t pqmf_G_off = 0;  // [N][taps+1]
+  size_t pqmf_fact_off = 0;   // factorised-synthesis table (pqmf.cu), valid when pqmf_fact
+  bool pqmf_fact = false;
   int hop_generator = 1;  // prod(upsample_factors)
   ttsb::HostStaging host;
 };

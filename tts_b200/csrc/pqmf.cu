@@ -11,11 +11,30 @@
 // at the fp32-FFMA ridge of a B200 (~11 FLOP/B), so the specialised kernel keeps both the FFMA
 // pipe and the LSU lean: x windows come from shared memory as aligned float4, coefficients as
 // one broadcast float4 per (band, offset), and stores are staged for full-line writes.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace ttsb {
 
 namespace {
+
+// Loads of data the PREVIOUS kernel of a programmatic-dependent-launch chain wrote.  They must stay behind
+// griddepcontrol.wait: a read-only-path load (__ldg / const __restrict__ -> ld.global.nc) is assumed by the
+// compiler to read immutable memory and may be hoisted above the wait (seen: the factorised kernel's first loads
+// moved up and read the sub-bands before the head kernel had written them).  volatile asm pins them.
+__device__ __forceinline__ float4 ld_after_wait4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_after_wait(const float* p) {
+  float v;
+  asm volatile("ld.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
 
 // ---- specialised N=4, K=63 (the only PQMF the reference instantiates: multiband_melgan_generator.py:24)
 constexpr int SQ_THREADS = 64;
@@ -25,7 +44,7 @@ constexpr int SQ_TILE = SQ_THREADS * SQ_QPT;     // 256 q per CTA -> 1024 output
 constexpr int SQ_HALO_L = 8;                     // window is q-7..q+8; 8 keeps float4 alignment
 constexpr int SQ_SMEM_Q = SQ_TILE + 16;          // 8 left + 8 right
 
-__global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float* __restrict__ x,
+__global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float* x,
                                                                       const float* __restrict__ G,
                                                                       float* __restrict__ y, int Ts) {
   __shared__ __align__(16) float sx[4][SQ_SMEM_Q];
@@ -55,14 +74,14 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
       const int k = e / (SQ_SMEM_Q / 4), s4 = e - k * (SQ_SMEM_Q / 4);
       const int q = q0 - SQ_HALO_L + 4 * s4;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (q >= 0 && q + 3 < Ts) v = __ldg(reinterpret_cast<const float4*>(xb + (int64_t)k * Ts + q));
+      if (q >= 0 && q + 3 < Ts) v = ld_after_wait4(xb + (int64_t)k * Ts + q);
       *reinterpret_cast<float4*>(&sx[k][4 * s4]) = v;       // q < 0 or q >= Ts: zero padding (whole vectors)
     }
   } else {
     for (int e = tid; e < 4 * SQ_SMEM_Q; e += SQ_THREADS) {
       const int k = e / SQ_SMEM_Q, s = e - k * SQ_SMEM_Q;
       const int q = q0 - SQ_HALO_L + s;
-      sx[k][s] = (q >= 0 && q < Ts) ? __ldg(xb + (int64_t)k * Ts + q) : 0.f;
+      sx[k][s] = (q >= 0 && q < Ts) ? ld_after_wait(xb + (int64_t)k * Ts + q) : 0.f;
     }
   }
   __syncthreads();
@@ -108,6 +127,110 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
   } else {
 #pragma unroll
     for (int i = 0; i < SQ_QPT; ++i)
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = acc[i][r];
+  }
+}
+
+// ---- factorised N=4, K=63 synthesis ------------------------------------------------------------------------
+// The reference's synthesis bank is cosine-modulated (pqmf.py:22-32): G[k][j] = q[j] * C[k][j] with
+// C[k][j] = 2 cos((2k+1) pi/8 (j - 30.5) - (-1)^k pi/4), which has C[k][j+8] = -C[k][j].  So
+//     y[4q+r] = sum_o w[r][o] * v[(4o+31-r) mod 8][q+o],   v[p][m] = sum_k C[k][p] x[k][m],
+//     w[r][o] = 4 q[j] (-1)^(j div 8), j = 4o+31-r, o = -7..8:
+// 8 modulated signals (32 MACs per sub-band sample = 8 per output) + a 16-tap FIR per output = 24 MACs per
+// output sample instead of 63.  Output r uses v[7-r] at even o and v[3-r] at odd o.  The table (C then w,
+// pqmf_factor_4x63 below) is built at plan creation and only if G really has this structure.
+constexpr int SF_THREADS = 128;
+constexpr int SF_TILE = SF_THREADS * 4;          // 512 q per CTA -> 2048 output samples
+constexpr int SF_WIN = SF_TILE + 16;             // v window: q0-8 .. q0+TILE+7
+
+__global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const float* x,
+                                                                           const float* __restrict__ tbl,
+                                                                           float* __restrict__ y, int Ts) {
+  __shared__ __align__(16) float sv[8][SF_WIN];
+  __shared__ __align__(16) float st[PQMF_FACT_TABLE];   // [p][k] modulation, then [p][8] FIR taps
+
+  const int tid = threadIdx.x;
+  const int b = blockIdx.y;
+  const int q0 = blockIdx.x * SF_TILE;
+  const float* xb = x + (int64_t)b * 4 * Ts;
+
+  pdl_launch_dependents();
+  if (tid < PQMF_FACT_TABLE) st[tid] = tbl[tid];
+  __syncthreads();
+  pdl_wait();   // the head's sub-band signals are complete from here on
+
+  // ---- phase 1: v[p][m] for the window.  Thread tid: 4 consecutive m (one float4 per band) ...
+  {
+    const int mw = 4 * tid;                       // window index of the first m
+    const int m = q0 - 8 + mw;
+    float4 xv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      xv[k] = (m >= 0 && m + 3 < Ts) ? ld_after_wait4(xb + (int64_t)k * Ts + m)
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);   // Ts % 4 == 0: whole vectors in or out
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const float4 c = *reinterpret_cast<const float4*>(&st[4 * p]);
+      float4 v;
+      v.x = fmaf(c.w, xv[3].x, fmaf(c.z, xv[2].x, fmaf(c.y, xv[1].x, c.x * xv[0].x)));
+      v.y = fmaf(c.w, xv[3].y, fmaf(c.z, xv[2].y, fmaf(c.y, xv[1].y, c.x * xv[0].y)));
+      v.z = fmaf(c.w, xv[3].z, fmaf(c.z, xv[2].z, fmaf(c.y, xv[1].z, c.x * xv[0].z)));
+      v.w = fmaf(c.w, xv[3].w, fmaf(c.z, xv[2].w, fmaf(c.y, xv[1].w, c.x * xv[0].w)));
+      *reinterpret_cast<float4*>(&sv[p][mw]) = v;
+    }
+    // ... plus one (m, p) pair of the 16-sample right halo
+    const int mh = SF_TILE + (tid >> 3), ph = tid & 7;
+    const int mg = q0 - 8 + mh;
+    float acc = 0.f;
+    if (mg >= 0 && mg < Ts) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc = fmaf(st[4 * ph + k], ld_after_wait(xb + (int64_t)k * Ts + mg), acc);
+    }
+    sv[ph][mh] = acc;
+  }
+  __syncthreads();
+
+  // ---- phase 2: 4 q x 4 phases per thread
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
+#pragma unroll
+  for (int p = 0; p < 8; ++p) {
+    float w[20];   // v[p][q_first-8 .. q_first+11]
+#pragma unroll
+    for (int u = 0; u < 5; ++u) {
+      const float4 t = *reinterpret_cast<const float4*>(&sv[p][4 * tid + 4 * u]);
+      w[4 * u + 0] = t.x; w[4 * u + 1] = t.y; w[4 * u + 2] = t.z; w[4 * u + 3] = t.w;
+    }
+    const float4 c0 = *reinterpret_cast<const float4*>(&st[32 + 8 * p]);
+    const float4 c1 = *reinterpret_cast<const float4*>(&st[32 + 8 * p + 4]);
+    const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    constexpr int dummy = 0;
+    (void)dummy;
+    const int r = p >= 4 ? 7 - p : 3 - p;        // the output phase this signal feeds
+    const int base = p >= 4 ? 2 : 1;             // window index of (i = 0, first o): o = -6 (even) or -7 (odd)
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i][r] = fmaf(c[e], w[i + base + 2 * e], acc[i][r]);
+  }
+
+  const int64_t Tout = 4 * (int64_t)Ts;
+  const int64_t t_first = (int64_t)(q0 + 4 * tid) * 4;
+  if (t_first >= Tout) return;
+  float* yt = y + (int64_t)b * Tout + t_first;
+  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+      asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(yt + 8 * h), "f"(acc[2 * h][0]),
+                   "f"(acc[2 * h][1]), "f"(acc[2 * h][2]), "f"(acc[2 * h][3]), "f"(acc[2 * h + 1][0]),
+                   "f"(acc[2 * h + 1][1]), "f"(acc[2 * h + 1][2]), "f"(acc[2 * h + 1][3])
+                   : "memory");
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int r = 0; r < 4; ++r)
         if (t_first + 4 * i + r < Tout) yt[4 * i + r] = acc[i][r];
@@ -160,6 +283,52 @@ __global__ void pqmf_analysis_kernel(const float* __restrict__ x, const float* _
 
 }  // namespace
 
+// Host side, at plan creation: G [4][63] -> the factorised kernel's table, or false when G is not the
+// cosine-modulated bank of pqmf.py:22-32 (a checkpoint may carry any buffer; the direct kernel then runs).
+bool pqmf_factor_4x63(const float* G, float* tbl) {
+  const double PI = 3.14159265358979323846;
+  double C[4][63], gmax = 0.0;
+  for (int k = 0; k < 4; ++k)
+    for (int j = 0; j < 63; ++j) {
+      C[k][j] = 2.0 * std::cos((2 * k + 1) * (PI / 8.0) * (j - 30.5) - ((k & 1) ? -1.0 : 1.0) * PI / 4.0);
+      gmax = std::max(gmax, std::fabs((double)G[k * 63 + j]));
+    }
+  double q[63];
+  for (int j = 0; j < 63; ++j) {
+    int kb = 0;
+    for (int k = 1; k < 4; ++k)
+      if (std::fabs(C[k][j]) > std::fabs(C[kb][j])) kb = k;
+    q[j] = (double)G[kb * 63 + j] / C[kb][j];
+    for (int k = 0; k < 4; ++k)
+      if (std::fabs((double)G[k * 63 + j] - q[j] * C[k][j]) > 1e-6 * gmax) return false;
+  }
+  for (int p = 0; p < 8; ++p)
+    for (int k = 0; k < 4; ++k) tbl[4 * p + k] = (float)C[k][p];
+  for (int p = 0; p < 8; ++p) {
+    const int r = p >= 4 ? 7 - p : 3 - p, o0 = p >= 4 ? -6 : -7;
+    for (int e = 0; e < 8; ++e) {
+      const int j = 4 * (o0 + 2 * e) + 31 - r;
+      tbl[32 + 8 * p + e] = (j >= 0 && j < 63) ? (float)(4.0 * q[j] * (((j / 8) & 1) ? -1.0 : 1.0)) : 0.f;
+    }
+  }
+  return true;
+}
+
+cudaError_t pqmf_synthesis_fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, float* y,
+                                       cudaStream_t stream) {
+  if (batch <= 0 || Ts <= 0) return cudaSuccess;
+  static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_fact_kernel,
+                                                        cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  if (carve != cudaSuccess) return carve;
+  const dim3 grid(ceil_div(Ts, SF_TILE), batch);
+  return launch_pdl(pqmf_synth_4x63_fact_kernel, grid, dim3(SF_THREADS), 0, stream, x, tbl, y, (int)Ts);
+}
+// usable when whole float4s of every band are in or out of range and aligned
+bool pqmf_fact_usable(const float* x, int64_t Ts) {
+  if (getenv("TTSB200_PQMF_DIRECT")) return false;   // debug: force the direct kernel
+  return (Ts & 3) == 0 && Ts < (1 << 29) && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+}
+
 cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int bands, int taps,
                                   int64_t Ts, float* y, cudaStream_t stream) {
   const int K = taps + 1, pad = taps / 2;
@@ -167,6 +336,11 @@ cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int
   if (batch <= 0 || Ts <= 0 || Tout <= 0) return cudaSuccess;
   if (bands == 4 && taps == 62 && Ts < (1 << 30)) {
     const dim3 grid(ceil_div(Ts, SQ_TILE), batch);
+    // 5.4 KB of static shared memory per 64-thread CTA: with the default carve-out only 21 CTAs fit an SM and cfg2's
+    // 23.5 CTAs per SM spill into a second, nearly empty wave; ask for the full carve-out (32 CTAs per SM).
+    static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_kernel,
+                                                          cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (carve != cudaSuccess) return carve;
     return launch_pdl(pqmf_synth_4x63_kernel, grid, dim3(SQ_THREADS), 0, stream, x, G, y, (int)Ts);
   } else {
     const dim3 grid(ceil_div(Tout, 256), batch);

@@ -427,6 +427,8 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     if (!to_out) {
       const int N = cfg.pqmf_bands;
       TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B, 8.0 * N * Lin * B, [&] {
+        if (plan->pqmf_fact && pqmf_fact_usable(headf, Lin))
+          return pqmf_synthesis_fact_launch(headf, Wf + plan->pqmf_fact_off, B, Lin, a->out, st);
         return pqmf_synthesis_launch(headf, Wf + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, st);
       }));
     }

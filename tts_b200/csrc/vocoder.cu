@@ -267,6 +267,8 @@ int forward_f32(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     if (!to_out) {
       const int N = cfg.pqmf_bands;
       TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B, 8.0 * N * Lin * B, [&] {
+        if (plan->pqmf_fact && pqmf_fact_usable(spare0, Lin))
+          return pqmf_synthesis_fact_launch(spare0, W + plan->pqmf_fact_off, B, Lin, a->out, st);
         return pqmf_synthesis_launch(spare0, W + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, st);
       }));
     }
@@ -357,6 +359,14 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
     const size_t n = (size_t)cfg->pqmf_bands * (cfg->pqmf_taps + 1);
     plan->pqmf_G_off = bb.alloc(n);
     std::memcpy(&bb.data[plan->pqmf_G_off], tensors[ti], n * sizeof(float));
+    if (cfg->pqmf_bands == 4 && cfg->pqmf_taps == 62) {
+      float tbl[ttsb::PQMF_FACT_TABLE];
+      if (ttsb::pqmf_factor_4x63(tensors[ti], tbl)) {
+        plan->pqmf_fact_off = bb.alloc(ttsb::PQMF_FACT_TABLE);
+        std::memcpy(&bb.data[plan->pqmf_fact_off], tbl, sizeof tbl);
+        plan->pqmf_fact = true;
+      }
+    }
     ti += 1;
   }
   plan->hop_generator = hop;
