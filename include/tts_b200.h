@@ -135,6 +135,13 @@ TTSB200_API int32_t ttsb200_pqmf_synthesis(const float* x, const float* G, int32
 TTSB200_API int32_t ttsb200_pqmf_analysis(const float* x, const float* H, int32_t batch, int32_t bands,
                               int32_t taps, int64_t T, float* y, void* stream);
 
+/* Host-only helper: factorises the 4-band / 63-tap synthesis bank G [4][63] (host pointer) into the table the
+ * generator's fast synthesis kernel uses — G[k][j] = q[j] * C[k][j] with the cosine modulation of pqmf.py:22-32,
+ * table = C[k][p] as [8][4] then the signed prototype taps as [8][8] (96 floats).  Returns 1 when G has that
+ * structure (ttsb200_plan_create then uses the 24-MAC kernel), 0 when it does not (direct 63-tap kernel), negative
+ * on error.  Exposed so that the factorisation can be checked against the oracle without a GPU. */
+TTSB200_API int32_t ttsb200_pqmf_factor_4x63(const float* G_host, float* table96_host);
+
 /* Per-launch timing.  Attach via args->profile; after the stream has been synchronised,
  * ttsb200_profile_read() returns one record per kernel launched since the last reset. */
 typedef struct ttsb200_launch_record {

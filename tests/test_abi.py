@@ -67,3 +67,35 @@ def test_sass_is_sm100a_only():
     out = subprocess.run(["cuobjdump", "-lelf", _lib.LIB_PATH], capture_output=True, text=True).stdout
     archs = set(re.findall(r"sm_(\d+a?)", out))
     assert archs == {"100a"}, archs
+
+
+def test_pqmf_factorisation_matches_oracle():
+    """Host-side factorisation behind the generator's fast synthesis kernel (pqmf.cu): on the reference's bank
+    (pqmf.py:19-32) the 8 modulated signals + 16-tap FIR reproduce PQMF.synthesis; a bank without the cosine
+    structure is refused (the direct 63-tap kernel then runs)."""
+    import numpy as np
+    import torch
+    from oracle.melgan_oracle import pqmf_filters, pqmf_synthesis
+
+    lib = _lib.load()
+    _, G, U = pqmf_filters()
+    g = np.ascontiguousarray(G[0].numpy(), dtype=np.float32)
+    tbl = np.zeros(96, np.float32)
+    assert lib.ttsb200_pqmf_factor_4x63(g.ctypes.data, tbl.ctypes.data) == 1
+    Ts = 96
+    x = torch.randn(2, 4, Ts, generator=torch.Generator().manual_seed(3))
+    ref = pqmf_synthesis(x, G, U)[:, 0].numpy()
+    xn = x.numpy().astype(np.float64)
+    C, W = tbl[:32].reshape(8, 4).astype(np.float64), tbl[32:].reshape(8, 8).astype(np.float64)
+    v = np.zeros((2, 8, Ts + 16))
+    v[:, :, 8:8 + Ts] = np.einsum("pk,bkm->bpm", C, xn)          # v[p][m] = sum_k C[k][p] x[k][m], window index m + 8
+    y = np.zeros((2, 4 * Ts))
+    for p in range(8):
+        r, base = (7 - p, 2) if p >= 4 else (3 - p, 1)            # output phase fed by signal p, first window index
+        for e in range(8):
+            y[:, r::4] += W[p, e] * v[:, p, base + 2 * e: base + 2 * e + Ts]
+    assert np.abs(y - ref).max() <= 5e-6 * np.abs(ref).max()
+    # a bank that is not cosine-modulated
+    rnd = np.random.default_rng(0).standard_normal((4, 63)).astype(np.float32)
+    assert lib.ttsb200_pqmf_factor_4x63(rnd.ctypes.data, tbl.ctypes.data) == 0
+    assert lib.ttsb200_pqmf_factor_4x63(None, tbl.ctypes.data) < 0

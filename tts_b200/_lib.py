@@ -79,6 +79,7 @@ SYMBOLS = {
                                                         ctypes.c_void_p]),
     "ttsb200_pqmf_synthesis": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32,
                                                 ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p]),
+    "ttsb200_pqmf_factor_4x63": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_void_p]),
     "ttsb200_pqmf_analysis": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32,
                                                ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p]),
     "ttsb200_profile_create": (ctypes.c_int32, [ctypes.POINTER(ctypes.c_void_p)]),

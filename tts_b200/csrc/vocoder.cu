@@ -529,6 +529,11 @@ int32_t ttsb200_pqmf_analysis(const float* x, const float* H, int32_t batch, int
   return 0;
 }
 
+int32_t ttsb200_pqmf_factor_4x63(const float* G_host, float* table96_host) {
+  if (!G_host || !table96_host) return fail(TTSB200_ERR_INVALID, "NULL argument");
+  return pqmf_factor_4x63(G_host, table96_host) ? 1 : 0;
+}
+
 int32_t ttsb200_profile_create(ttsb200_profile** out_profile) {
   if (!out_profile) return fail(TTSB200_ERR_INVALID, "NULL argument");
   *out_profile = new ttsb200_profile();
