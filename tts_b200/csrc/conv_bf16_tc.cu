@@ -354,6 +354,8 @@ constexpr int CP_MAX_SLOTS = 6;
 constexpr int CP_CHUNK_PLANES = 8;   // 64 channels per activation chunk
 // A chunk is 8 small plane copies; their issue cost (~450 + 90 per copy cycles of the issuing warp, see
 // tests/cuda/ingest_probe.cu) exceeds the chunk's MMA time, so two warps issue alternate chunks.
+// (Measured alternative that lost: ONE 4-D tensor-map copy per chunk, box {8 channels, rows, 8 planes, 1} — the
+// layout's 16-byte inner extent makes the TMA unit fetch 16 bytes per request: convT@6 27.1 -> 29.5 us.)
 constexpr int NTP = NT + 32;
 
 __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ TcConvParams p, const int nslots,

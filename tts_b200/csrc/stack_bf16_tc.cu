@@ -92,6 +92,9 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   constexpr bool SPLIT_E2 = CP >= 96;
   // ... and run epilogue 2 in 16-column chunks (see there); narrow stages do it all at once.
   constexpr bool CHUNKED_E2 = CP >= 96;
+  // ... and stage the next item (raw x -> XR, lrelu(x) -> XA) while the fused tail's MMAs run.  On the narrow stages
+  // the extra live state costs more than the overlap gains (measured: +4..6 %).
+  constexpr bool EARLY_STAGE = TAIL != 0 && CP >= 96;
   static_assert(!RING || KT == 1, "ring mode handles one tile per CTA");
   constexpr int NK = CP / RING_KB;                       // chunks per tap
   constexpr uint32_t SLOT_BYTES = RING_KB * CP * 2;
@@ -535,6 +538,49 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     Tracer trw = make_tracer(p.trace, 1 + KT + warp, lane == 0 && !DBG(512));   // per-warp arrival times
     uint32_t n_d1 = 0;                          // completed d1_full rounds (blocks, plus the fused head)
 
+    // First half of an item's prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place in XA.  It touches
+    // neither D1 nor D2, so in kernels with a fused tail it runs for item it+1 while item it's tail MMAs execute
+    // (its x tile was prefetched a whole item earlier); only the accumulators' bias rows and the publish remain
+    // between the tail epilogue and the next item's first dilated conv.
+    auto stage_item = [&](int it_) {
+      const int item_ = blockIdx.x + it_ * gridDim.x;
+      const int b_ = item_ / p.n_chains, chain_ = item_ - b_ * p.n_chains;
+      const int g0_ = chain_ * V - SD;
+      uint8_t* xa_ = sXA + (size_t)(it_ & 1) * xa_bytes + (size_t)(c0 / 8) * plane_bytes;
+      const int reach_ = G > p.out.halo ? G : p.out.halo;
+      const bool edge_ = g0_ <= reach_ || g0_ + TR + reach_ >= L - 1;
+      mbar_wait_relaxed(&bars.x_full[it_ & 1], (it_ >> 1) & 1);
+      uint32_t w[CW / 2];
+      const uint8_t* src = xa_ + (size_t)(G + t * 128 + m) * 16;
+#pragma unroll
+      for (int pl = 0; pl < CW / 8; ++pl) {
+        const uint4 u = *reinterpret_cast<const uint4*>(src + (size_t)pl * plane_bytes);
+        w[4 * pl] = u.x; w[4 * pl + 1] = u.y; w[4 * pl + 2] = u.z; w[4 * pl + 3] = u.w;
+      }
+      tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+#pragma unroll
+      for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
+      auto rows = [&](int r) {
+        uint8_t* dst = xa_ + (size_t)(G + r) * 16;
+#pragma unroll
+        for (int pl = 0; pl < CW / 8; ++pl)
+          *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) =
+              make_uint4(w[4 * pl], w[4 * pl + 1], w[4 * pl + 2], w[4 * pl + 3]);
+      };
+      if (!edge_) {
+        rows(t * 128 + m);
+      } else {
+        const int tau = g0_ + t * 128 + m;
+        if (tau >= 0 && tau < L) {
+          rows(tau - g0_);
+          if (tau >= 1 && tau <= G && -tau - g0_ >= -G) rows(-tau - g0_);
+          const int back = L - 1 - tau;
+          if (back >= 1 && back <= G && L - 1 + back - g0_ < TR + G) rows(L - 1 + back - g0_);
+        }
+      }
+    };
+    bool staged = false;   // the current item's first prologue half already ran (during the previous item's tail)
+
     int gb = 0;
     for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
       const int item = blockIdx.x + it * gridDim.x;
@@ -659,6 +705,23 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       };
 
       // ---- prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place; accumulators <- block 0 biases
+      if (EARLY_STAGE) {
+        if (!staged) stage_item(it);
+        tr(200);
+        init_acc(tlane, s_bias[0][0]);
+        if (!SPLIT_E2) init_acc(tlane + CP, s_bias[0][1]);
+        tmem_wait_st();
+        fence_proxy_async();
+        tc_fence_before();
+        mbar_arrive(&bars.xa_ready[t]);
+        if (SPLIT_E2) {
+          init_acc(tlane + CP, s_bias[0][1]);
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(&bars.xr_ready[t]);
+        }
+        tr(201);
+      } else {
       mbar_wait_relaxed(&bars.x_full[buf], (it >> 1) & 1);
       tr(200);
       {
@@ -691,6 +754,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           mbar_arrive(&bars.xr_ready[t]);
         }
         tr(201);
+      }
       }
 
       for (int blk = 0; blk < nb; ++blk, ++gb) {
@@ -870,6 +934,10 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             tr(222);
           }
         }
+      }
+      if (EARLY_STAGE) {
+        staged = blockIdx.x + (it + 1) * gridDim.x < n_items;
+        if (staged) stage_item(it + 1);
       }
       if (head) {
         // ---- epilogue 3: tanh of the head accumulator -> fp32 [batch][head_ch][L]
