@@ -258,16 +258,17 @@ def gpu_arm(args):
              "frac_of_bf16_peak": value / world * flops_per_sample / 1e12 / peaks["bf16_tflops_sustained"]}
 
     # e2e: public API with HOST buffers.  Every step uploads its pinned mel batch, runs inference() and reads
-    # the waveform back into pinned memory (inference_to_host); steps alternate between two streams so one
-    # step's copies overlap the other's kernels.  Wall clock around K steps, synchronised on both sides.
+    # the waveform back into pinned memory (inference_to_host); steps rotate over NS streams so one
+    # step's copies overlap the others' kernels.  Wall clock around K steps, synchronised on both sides.
     ke = max(3, args.steps)
     host_pool = [torch.randn(BATCH, 80, FRAMES, generator=g).pin_memory() for _ in range(4)]
-    host_out = [torch.empty((BATCH, 1, n_out), dtype=torch.float32).pin_memory() for _ in range(2)]
-    streams = [torch.cuda.Stream(dev) for _ in range(2)]
-    events = [None, None]
+    NS = 3   # in-flight steps: one stream's H2D + D2H (0.09 + 0.27 ms) is longer than a step's kernels, two streams stall
+    host_out = [torch.empty((BATCH, 1, n_out), dtype=torch.float32).pin_memory() for _ in range(NS)]
+    streams = [torch.cuda.Stream(dev) for _ in range(NS)]
+    events = [None] * NS
 
     def e2e_step(i):
-        s = i % 2
+        s = i % NS
         with torch.cuda.stream(streams[s]):
             if events[s] is not None:
                 events[s].synchronize()            # the host buffer of this slot has been consumed
@@ -284,7 +285,7 @@ def gpu_arm(args):
     te = allreduce_max(time.perf_counter() - t0, world, dev)
     e2e = {"value": world * samples_per_step * ke / te, "unit": "samples/s", "h2d_bytes_per_step": per_batch,
            "d2h_bytes_per_step": host_out[0].numel() * 4, "steps": ke, "ms_per_step": te / ke * 1e3,
-           "api": "MultibandMelganGenerator.inference_to_host(pinned cpu mel, out=pinned cpu wav), 2 streams"}
+           "api": f"MultibandMelganGenerator.inference_to_host(pinned cpu mel, out=pinned cpu wav), {NS} streams"}
     # the reference callers' exact pattern, for comparison: inference(cpu mel).cpu() (pageable result, blocking)
     kb = max(3, min(args.steps, 10))
     model.inference(host_pool[0]).cpu()
