@@ -283,6 +283,23 @@ def test_bf16_fused_head_matches_unfused(case):
     assert snr_db(ref, fused) >= snr_db(ref, unfused.cpu()) - 1.0
 
 
+@pytest.mark.parametrize("grid", [1, 3])
+def test_bf16_persistent_ctas_walk_many_items(grid, monkeypatch):
+    """The fused-stack kernel is persistent: a CTA walks `items / grid` work items, overlapping one item's fused tail
+    with the staging of the next (edge items included).  Small inputs normally give every CTA a single item, so
+    the grid is capped here; the waveform must not depend on how items are dealt to CTAs."""
+    cls, kw, _, _, p = CASES[1]                      # MB-MelGAN defaults: all three fused tails in one model
+    m, spec, sd = default_init(cls, kw)
+    m.inference_padding = p
+    m.precision = "bf16"
+    mel = torch.randn(3, spec.in_channels, 37, generator=torch.Generator().manual_seed(23))
+    free = m.inference(mel).cpu()
+    monkeypatch.setenv("TTSB200_STACK_MAX_GRID", str(grid))
+    capped = m.inference(mel).cpu()
+    assert torch.equal(free, capped)
+    assert snr_db(generator_inference(spec, sd, mel, p), capped) >= BF16_SNR
+
+
 def test_bf16_full_size_cfg2_and_golden(golden):
     g = golden("mb_cfg2_item")
     m, spec, sd = default_init("multiband", {})

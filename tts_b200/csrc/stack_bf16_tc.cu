@@ -28,6 +28,7 @@
 // owns tile t (prologue, both epilogues of every block), one warp per TMEM lane quarter and channel split.
 // Tiles therefore advance as independent chains: the latency of one tile's epilogue (barrier -> tcgen05.ld ->
 // math -> tcgen05.st -> barrier) hides behind the MMAs and epilogues of the other tiles.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -1128,7 +1129,9 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int items = p.n_chains * batch;
   const int slots = sms * tc_stack_ctas_per_sm(p.cp);
-  const int grid = items < slots ? items : slots;
+  int grid = items < slots ? items : slots;
+  // test hook: few CTAs, so that each walks many items (item transitions, staging of the next item) on small inputs
+  if (const char* g = getenv("TTSB200_STACK_MAX_GRID")) grid = std::max(1, std::min(grid, atoi(g)));
   if (const char* dbg = getenv("TTSB200_STACK_DEBUG")) p.debug = atoi(dbg);
   p.trace = trace_begin(stream);
   const cudaError_t rc = dispatch(p, smem, grid, stream);
