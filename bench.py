@@ -374,7 +374,8 @@ def streaming_arm(args):
     m = m.to(dev).eval()
     m.freeze()
     chunk, rate = 20, 24000
-    sv = StreamingVocoder(m, chunk_frames=chunk)
+    use_graph = not os.environ.get("TTSB200_STREAM_NO_GRAPH")
+    sv = StreamingVocoder(m, chunk_frames=chunk, use_graph=use_graph)
     n_chunks = max(50, args.steps * 10)
     mel = torch.randn(1, 80, chunk * (n_chunks + args.warmup + 4), generator=torch.Generator().manual_seed(MEL_SEED))
     host = mel.pin_memory()
@@ -398,7 +399,8 @@ def streaming_arm(args):
             "config": {"workload": "BASELINE config 5: FullbandMelganGenerator(upsample_factors=(5,5,4,3)) hop 300, "
                                    f"24 kHz, stream of [1,80,{chunk}] chunks (250 ms), context {sv.ctx} frames per side, "
                                    "latency = host chunk in -> 6000 samples back on the host",
-                       "chunk_frames": chunk, "context_frames": sv.ctx, "samples_per_chunk": chunk * sv.hop}}
+                       "chunk_frames": chunk, "context_frames": sv.ctx, "samples_per_chunk": chunk * sv.hop,
+                       "launch": "CUDA graph per window shape" if use_graph else "kernel by kernel"}}
     print(json.dumps(line))
 
 

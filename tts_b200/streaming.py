@@ -17,14 +17,60 @@ import torch.nn.functional as F
 from .longform import hop_length, receptive_halo_frames
 
 
+class GraphedInference:
+    """``generator.inference`` (padding 0) replayed from a CUDA graph per window shape.
+
+    A streaming window is tiny (tens of frames): its ten-odd kernel launches and the allocator calls around them
+    cost more host time than the kernels take on the device.  Every steady-state window has the same shape, so the
+    whole forward — the C-ABI launches included, they go to the capturing stream like any other launch — is captured
+    once per shape and replayed; the first chunks of a stream and the flush have their own (also cached) shapes.
+    The result is copied out of the graph's static buffer, so callers may keep it."""
+
+    def __init__(self, generator, max_graphs=8):
+        self.g = generator
+        self.max_graphs = max_graphs
+        self._graphs = {}
+
+    def _capture(self, shape, device):
+        static_in = torch.zeros(shape, dtype=torch.float32, device=device)
+        saved = self.g.inference_padding
+        self.g.inference_padding = 0
+        try:
+            side = torch.cuda.Stream(device)
+            side.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(side):          # warm-up off the capture: plan creation, attribute calls, workspace
+                self.g.inference(static_in)
+            torch.cuda.current_stream(device).wait_stream(side)
+            torch.cuda.synchronize(device)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                static_out = self.g.inference(static_in)
+        finally:
+            self.g.inference_padding = saved
+        return graph, static_in, static_out
+
+    def __call__(self, mel):
+        key = (tuple(mel.shape), mel.device)
+        entry = self._graphs.get(key)
+        if entry is None:
+            if len(self._graphs) >= self.max_graphs:
+                self._graphs.pop(next(iter(self._graphs)))
+            entry = self._graphs[key] = self._capture(tuple(mel.shape), mel.device)
+        graph, static_in, static_out = entry
+        static_in.copy_(mel, non_blocking=True)
+        graph.replay()
+        return static_out.clone()
+
+
 class StreamingVocoder:
     """Feed mel frames with ``feed``; collect waveform chunks; call ``flush`` at the end of the stream.
 
     generator: a tts_b200 generator on a CUDA device (eval).  chunk_frames: frames per emitted chunk.
     context: frames of left/right context (default: the receptive field, ``receptive_halo_frames``).
+    use_graph: replay each window shape from a CUDA graph (``GraphedInference``) instead of launching kernel by kernel.
     """
 
-    def __init__(self, generator, chunk_frames=20, context=None, infer_fn=None):
+    def __init__(self, generator, chunk_frames=20, context=None, infer_fn=None, use_graph=False):
         self.g = generator
         self.chunk = int(chunk_frames)
         self.ctx = receptive_halo_frames(generator) if context is None else int(context)
@@ -32,7 +78,7 @@ class StreamingVocoder:
             raise ValueError("chunk_frames must be >= 1 and context >= 0")
         self.hop = hop_length(generator)
         self.pad = int(generator.inference_padding)
-        self._infer = infer_fn or self._infer_unpadded
+        self._infer = infer_fn or (GraphedInference(generator) if use_graph else self._infer_unpadded)
         self.reset()
 
     def reset(self):
