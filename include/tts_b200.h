@@ -32,7 +32,7 @@ extern "C" {
 #define TTSB200_API
 #endif
 
-#define TTSB200_ABI_VERSION 1
+#define TTSB200_ABI_VERSION 2
 #define TTSB200_MAX_STAGES 8
 
 typedef enum ttsb200_status {
@@ -66,6 +66,14 @@ typedef struct ttsb200_generator_config {
   float act_slope;          /* LeakyReLU slope (0.2)                                             */
 } ttsb200_generator_config;
 
+/* Element type of the waveform a forward call writes.  Every reference caller ends in a 16-bit WAV
+ * (TTS/utils/audio.py:338-340 save_wav -> int16 after a max-normalise); fp16 keeps |wav| <= 1 to a
+ * relative 2^-11 and halves the device->host bytes of the result. */
+typedef enum ttsb200_out_dtype {
+  TTSB200_OUT_F32 = 0,
+  TTSB200_OUT_F16 = 1
+} ttsb200_out_dtype;
+
 typedef struct ttsb200_plan ttsb200_plan;       /* immutable after creation; shareable across threads */
 typedef struct ttsb200_profile ttsb200_profile; /* per-launch CUDA-event timings; one user at a time  */
 
@@ -76,7 +84,8 @@ typedef struct ttsb200_forward_args {
   int32_t pad;              /* inference_padding: replicate-pad frames per side                  */
                             /* (melgan_generator.py:85-88); 0 for forward()                      */
   int32_t precision;        /* ttsb200_precision                                                 */
-  float* out;               /* device, [batch, 1 or out_channels, ttsb200_output_length()] fp32  */
+  void* out;                /* device, [batch, 1 or out_channels, ttsb200_output_length()],      */
+                            /*   fp32, or fp16 when out_dtype == TTSB200_OUT_F16                 */
   void* workspace;          /* device scratch, >= ttsb200_workspace_bytes(), 256-byte aligned    */
   size_t workspace_bytes;
   void* stream;             /* cudaStream_t                                                      */
@@ -85,6 +94,7 @@ typedef struct ttsb200_forward_args {
   const int32_t* tap_layers;/*   the indexing of bin/convert_melgan_torch_to_tf.py:89-101)       */
   float* const* tap_out;    /*   each device [batch, C_i, L_i] fp32                              */
   ttsb200_profile* profile; /* optional                                                          */
+  int32_t out_dtype;        /* ttsb200_out_dtype of `out` (taps are always fp32)                 */
 } ttsb200_forward_args;
 
 TTSB200_API int32_t ttsb200_abi_version(void);

@@ -18,6 +18,7 @@ from tts_b200.vocoder.models.multiband_melgan_generator import MultibandMelganGe
 
 pytestmark = pytest.mark.gpu
 F32_TOL = 1e-5
+BF16_SNR = 40.0
 CLS = {"melgan": MelganGenerator, "multiband": MultibandMelganGenerator, "fullband": FullbandMelganGenerator}
 
 
@@ -173,9 +174,10 @@ def test_full_size_properties_cfg2():
     assert torch.equal(one[0], out[5])
     # determinism
     assert torch.equal(m.inference(mel), out)
-    # oracle on one item
-    ref = generator_inference(spec, sd, mel[5:6].cpu(), 2)
-    assert float((one.cpu() - ref).abs().max()) <= F32_TOL
+    # the whole batch against the CPU oracle, item by item (the full-size config, not a sample of it)
+    ref = generator_inference(spec, sd, mel.cpu(), 2)
+    err = (out.cpu() - ref).abs().amax(dim=(1, 2))
+    assert float(err.max()) <= F32_TOL, err.tolist()
     # shift equivariance away from the edges: delaying the mel by 3 frames delays the audio by 3*256
     m.inference_padding = 0
     a = m.inference(mel[:1, :, 0:400])
@@ -190,6 +192,97 @@ def test_host_buffer_entry_point():
     dev = m.inference(mel).cpu()
     host = m._get_engine().forward_host(mel, m.inference_padding)
     assert torch.equal(dev, host)
+
+
+def test_host_buffer_entry_point_multichannel_without_pqmf():
+    """A generator with out_channels > 1 and no PQMF writes [B, out_channels, L]: the host entry point must size its
+    device buffer and the read-back for all channels."""
+    kw = {"in_channels": 8, "out_channels": 4, "base_channels": 32, "upsample_factors": (2, 3), "num_res_blocks": 2}
+    m, spec, sd = build("melgan", kw, seed=6)
+    mel = torch.randn(2, 8, 21)
+    ref = generator_inference(spec, sd, mel, 2)
+    dev = m.inference(mel).cpu()
+    host = m._get_engine().forward_host(mel, m.inference_padding)
+    assert host.shape == ref.shape == (2, 4, 25 * 6)
+    assert torch.equal(dev, host)
+    assert float((host - ref).abs().max()) <= F32_TOL
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_inference_to_host(precision):
+    """inference_to_host: pinned result, valid once the returned event has completed, equal to inference().cpu();
+    the caller's buffer is reused via out=; the fp16 form is the fp32 waveform rounded once (<= 2^-11 relative)."""
+    m, spec, sd = default_init("multiband", {})
+    m.precision = precision
+    mel = torch.randn(2, 80, 40, generator=torch.Generator().manual_seed(41)).pin_memory()
+    want = m.inference(mel).cpu()
+    got, ev = m.inference_to_host(mel)
+    assert got.is_pinned() and got.dtype == torch.float32 and got.shape == want.shape
+    ev.synchronize()
+    assert ev.query() and torch.equal(got, want)
+    buf = torch.zeros_like(got).pin_memory()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):                                  # on a side stream: the event belongs to that stream
+        again, ev2 = m.inference_to_host(mel, out=buf)
+    assert again is buf
+    ev2.synchronize()
+    assert torch.equal(buf, want)
+    half, ev3 = m.inference_to_host(mel, dtype=torch.float16)
+    ev3.synchronize()
+    assert half.dtype == torch.float16 and half.is_pinned() and half.shape == want.shape
+    assert torch.equal(half, want.half())                       # the same fp32 value, rounded to nearest once
+    assert float((half.float() - want).abs().max()) <= 2.0 ** -11 * float(want.abs().max()) + 1e-7
+    # fp16 out on a generator without PQMF (conversion kernel) and on the stand-alone sub-band output
+    g, _, _ = default_init("melgan", {"in_channels": 8, "base_channels": 32, "upsample_factors": (2, 3),
+                                      "num_res_blocks": 2})
+    g.precision = precision
+    x = torch.randn(1, 8, 19)
+    y32 = g.inference(x)
+    y16, e = g.inference_to_host(x, dtype=torch.float16)
+    e.synchronize()
+    assert torch.equal(y16, y32.cpu().half())
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_module_on_a_non_current_device():
+    """The reference allows a generator on cuda:1 while cuda:0 is the current device (inference() moves the input to
+    the weights' device, melgan_generator.py:84): launches, attributes and the SM-count query follow the plan."""
+    assert torch.cuda.current_device() == 0
+    for prec in ("fp32", "bf16"):
+        m, spec, sd = default_init("multiband", {})
+        m = m.to("cuda:1")
+        m.precision = prec
+        mel = torch.randn(1, 80, 33, generator=torch.Generator().manual_seed(43))
+        out = m.inference(mel)
+        assert out.device == torch.device("cuda", 1) and torch.cuda.current_device() == 0
+        ref = generator_inference(spec, sd, mel, 2)
+        if prec == "fp32":
+            assert float((out.cpu() - ref).abs().max()) <= F32_TOL
+        else:
+            assert snr_db(ref, out.cpu()) >= BF16_SNR
+        sub = m.pqmf_layer.synthesis(torch.randn(1, 4, 64, device="cuda:1"))
+        assert sub.device == torch.device("cuda", 1)
+
+
+def test_workspaces_are_bounded_across_threads():
+    """One scratch tensor per launch stream (not per thread): request threads on the default stream share one."""
+    import threading
+    m, spec, sd = build("melgan", {"in_channels": 8, "base_channels": 32, "upsample_factors": (2, 3),
+                                   "num_res_blocks": 2}, seed=2)
+    mel = torch.randn(1, 8, 30)
+    want = m.inference(mel).cpu()
+    outs = []
+    ts = [threading.Thread(target=lambda: outs.append(m.inference(mel).cpu())) for _ in range(12)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert all(torch.equal(o, want) for o in outs)
+    eng = m._get_engine()
+    assert len(eng._ws) == 1
+    for _ in range(eng.MAX_WORKSPACES + 4):                     # many streams: the cache stays bounded
+        with torch.cuda.stream(torch.cuda.Stream()):
+            m.inference(mel)
+    torch.cuda.synchronize()
+    assert len(eng._ws) <= eng.MAX_WORKSPACES
 
 
 def test_streams_and_threads():
@@ -220,8 +313,11 @@ def test_streams_and_threads():
 #       noise, per layer and end to end — this is the kernel-correctness check;
 #   (2) vs the fp32 reference on the reference's own default-init weights: SNR >= 40 dB (north_star).
 # ------------------------------------------------------------------------------------------------
-BF16_SNR = 40.0
-NORTH_STAR = 3   # CASES[:3] are the BASELINE.json models (MelGAN cfg1, MB-MelGAN defaults): the 40 dB bar applies
+# CASES[:5] are real models (MelGAN cfg1, MB-MelGAN defaults, the cfg5 FB-MelGAN (5,5,4,3), the shipped [8,4,2]x4
+# config): the 40 dB bar is asserted for all of them.  CASES[5:] are toy widths (C0 = 32 / 40) that exist to reach
+# odd kernel paths; the CPU emulation of BF16 rounding itself sits at 39.3 dB on CASES[5] (8 channels of 16 are
+# padding, outputs ~1e-2), so those two are held to the emulation only.
+NORTH_STAR = 5
 
 
 def default_init(cls, kw):
@@ -265,6 +361,69 @@ def test_bf16_end_to_end_and_per_layer(case, init):
         assert got >= BF16_SNR, got
 
 
+def edge_max_abs(a, b, n):
+    """max |a - b| over the first and last n samples: a whole-tensor SNR can hide a few wrong rows at a sequence end
+    (reflect mirrors, the fused tails' zero rows)."""
+    d = (a - b).abs()
+    return float(torch.maximum(d[..., :n].max(), d[..., -n:].max()))
+
+
+@pytest.mark.parametrize("case", range(len(CASES)))
+def test_bf16_per_layer_on_the_fused_schedule(case):
+    """Per-layer parity on the schedule the bench times: taps of tensors the fused kernels write themselves (projection,
+    every transposed-conv output incl. the ones the TAIL=2 stack kernels produce, the head output of the TAIL=1
+    kernel) leave fusion ON — checked by the launch names — and are compared with the BF16 emulation per layer, with a
+    max-abs check at the sequence ends on top of the SNR."""
+    from oracle.bf16_emulation import generator_inference_bf16
+    from tts_b200.engine import Profile
+    from tts_b200 import _lib
+    cls, kw, B, T, p = CASES[case]
+    m, spec, sd = default_init(cls, kw)
+    m.inference_padding = p
+    m.precision = "bf16"
+    mel = torch.randn(B, spec.in_channels, T, generator=torch.Generator().manual_seed(29))
+    taps_emu = {}
+    emu = generator_inference_bf16(spec, sd, mel, p, taps=taps_emu)
+    ref = generator_inference(spec, sd, mel, p)
+    layers = [1] + [spec.idx_upsample(s) for s in range(spec.n_stages)] + [spec.idx_head() + 1]
+    prof = Profile()
+    skip = cls != "multiband"                                # MultibandMelganGenerator.inference runs PQMF synthesis
+    out, taps = m._run(mel, p, skip, tap_layers=layers, profile=prof)
+    torch.cuda.synchronize()
+    names = [r["name"] for r in prof.read()]
+    eng = m._get_engine()
+    assert len(names) == eng.launch_count(_lib.BF16, skip_pqmf=skip), names      # same launches as inference()
+    plain = Profile()
+    m._run(mel, p, skip, profile=plain)
+    torch.cuda.synchronize()
+    assert names == [r["name"] for r in plain.read()]
+    inherent = snr_db(ref, emu)
+    for i in layers:
+        got, want = taps[i].cpu(), taps_emu[i]
+        assert snr_db(want, got) >= min(45.0, inherent), (i, snr_db(want, got))
+        scale = float(want.abs().max())
+        assert edge_max_abs(want, got, 64) <= 0.02 * scale + 1e-6, (i, edge_max_abs(want, got, 64), scale)
+    assert snr_db(emu, out.cpu()) >= inherent - 3.0
+    assert edge_max_abs(emu, out.cpu(), 256) <= 0.02 * float(emu.abs().max()) + 1e-6
+    if case < NORTH_STAR:
+        assert snr_db(ref, out.cpu()) >= BF16_SNR
+
+
+def test_bf16_chain_seams_max_abs():
+    """A sequence much longer than one work item (V rows): every chain seam of every stage lies inside the output.
+    Compared with the BF16 emulation sample by sample (max-abs), not only by SNR."""
+    from oracle.bf16_emulation import generator_inference_bf16
+    m, spec, sd = default_init("multiband", {})
+    m.precision = "bf16"
+    mel = torch.randn(1, 80, 150, generator=torch.Generator().manual_seed(31))
+    emu = generator_inference_bf16(spec, sd, mel, 2)
+    out = m.inference(mel).cpu()
+    d = (out - emu).abs()
+    # accumulation-order flips of single bf16 roundings: a wrong halo row would be O(signal)
+    assert float(d.max()) <= 0.03 * float(emu.abs().max()), (float(d.max()), float(emu.abs().max()))
+    assert snr_db(emu, out) >= 45.0
+
+
 @pytest.mark.parametrize("case", range(len(CASES)))
 def test_bf16_fused_head_matches_unfused(case):
     """inference() folds the output head into the last stage's kernel; inference_with_taps() runs the stand-alone
@@ -276,7 +435,7 @@ def test_bf16_fused_head_matches_unfused(case):
     m.precision = "bf16"
     mel = torch.randn(B, spec.in_channels, T, generator=torch.Generator().manual_seed(17))
     fused = m.inference(mel).cpu()
-    unfused, _ = m.inference_with_taps(mel, [1])
+    unfused, _ = m.inference_with_taps(mel, [spec.idx_stack(s) for s in range(spec.n_stages)])   # stack taps: no tails
     ref = generator_inference(spec, sd, mel, p)
     assert fused.shape == ref.shape
     assert snr_db(unfused.cpu(), fused) >= 45.0
@@ -294,8 +453,12 @@ def test_bf16_persistent_ctas_walk_many_items(grid, monkeypatch):
     m.precision = "bf16"
     mel = torch.randn(3, spec.in_channels, 37, generator=torch.Generator().manual_seed(23))
     free = m.inference(mel).cpu()
+    # the hook is read once, at plan creation (nothing on the launch path calls getenv): build a second module
     monkeypatch.setenv("TTSB200_STACK_MAX_GRID", str(grid))
-    capped = m.inference(mel).cpu()
+    m2, _, _ = default_init(cls, kw)
+    m2.inference_padding = p
+    m2.precision = "bf16"
+    capped = m2.inference(mel).cpu()
     assert torch.equal(free, capped)
     assert snr_db(generator_inference(spec, sd, mel, p), capped) >= BF16_SNR
 
@@ -316,9 +479,13 @@ def test_bf16_full_size_cfg2_and_golden(golden):
     assert bool(torch.isfinite(a).all())
     assert torch.equal(m.inference(melb[3:4])[0], a[3])
     assert torch.equal(m.inference(melb), a)
+    # the whole 16-item batch against the CPU oracle (reference default-init weights): every item >= 40 dB
+    ref = generator_inference(spec, sd, melb.cpu(), 2)
+    snrs = [snr_db(ref[i], a[i].cpu()) for i in range(16)]
+    assert min(snrs) >= BF16_SNR, snrs
     m.precision = "fp32"
     f = m.inference(melb)
-    assert snr_db(f.cpu(), a.cpu()) >= BF16_SNR
+    assert float((f.cpu() - ref).abs().max()) <= F32_TOL
 
 
 def test_bf16_melgan_cfg1_golden(golden):

@@ -8,9 +8,10 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libtts_b200.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 MAX_STAGES = 8
 F32, BF16 = 0, 1
+OUT_F32, OUT_F16 = 0, 1
 PRECISIONS = {"fp32": F32, "f32": F32, "float32": F32, "bf16": BF16, "bfloat16": BF16}
 
 
@@ -46,6 +47,7 @@ class ForwardArgs(ctypes.Structure):
         ("tap_layers", ctypes.POINTER(ctypes.c_int32)),
         ("tap_out", ctypes.POINTER(ctypes.c_void_p)),
         ("profile", ctypes.c_void_p),
+        ("out_dtype", ctypes.c_int32),
     ]
 
 

@@ -13,6 +13,7 @@
 //
 // Warp roles (192 threads): warp 0 = copy producer + TMEM owner, warp 1 = MMA issuer (one
 // thread), warps 2..5 = LeakyReLU prologue in shared memory + epilogue (one TMEM lane quarter each).
+#include <atomic>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -581,8 +582,7 @@ namespace {
 // Ring depth of the persistent variant for this launch; 0 = not eligible (two sources, in-kernel LeakyReLU,
 // fp32 output, or weights that do not fit beside a useful ring).
 int convp_slots(const TcConvParams& p, size_t* smem_bytes) {
-  static const bool off = getenv("TTSB200_CONV_PERSISTENT") && atoi(getenv("TTSB200_CONV_PERSISTENT")) == 0;
-  if (off || p.nsrc != 1 || p.src[0].lrelu || p.out_mode != 0 || (p.src[0].planes & 1)) return 0;
+  if (p.nsrc != 1 || p.src[0].lrelu || p.out_mode != 0 || (p.src[0].planes & 1)) return 0;
   size_t w = 0;
   for (int g = 0; g < p.ngroups; ++g) {
     if (p.grp[g].ncols > 256) return 0;
@@ -601,38 +601,57 @@ int convp_slots(const TcConvParams& p, size_t* smem_bytes) {
 }
 }  // namespace
 
-cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, cudaStream_t stream) {
+TcLaunchCtx tc_launch_ctx(int device) {
+  TcLaunchCtx c;
+  c.device = device;
+  cudaDeviceGetAttribute(&c.sms, cudaDevAttrMultiProcessorCount, device);
+  auto env_int = [](const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+  };
+  c.stack_max_grid = env_int("TTSB200_STACK_MAX_GRID", 0);
+  c.stack_debug = env_int("TTSB200_STACK_DEBUG", 0);
+  c.conv_debug = env_int("TTSB200_CONV_DEBUG", 0);
+  c.conv_persistent = env_int("TTSB200_CONV_PERSISTENT", 1);
+  c.pqmf_direct = getenv("TTSB200_PQMF_DIRECT") ? 1 : 0;
+  c.trace_file = getenv("TTSB200_STACK_TRACE");
+  return c;
+}
+
+cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCtx& ctx, cudaStream_t stream) {
   TcConvParams p = p_in;
+  // cudaFuncSetAttribute is per device and costs a driver call: once per device, not per launch
+  static std::atomic<uint64_t> attr_done{0};
+  const uint64_t bit = 1ull << (ctx.device & 63);
+  if (!(attr_done.load(std::memory_order_acquire) & bit)) {
+    cudaError_t e = cudaFuncSetAttribute(tc_convp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    if (e != cudaSuccess) return e;
+    attr_done.fetch_or(bit, std::memory_order_release);
+  }
+  p.debug = ctx.conv_debug;
   {
     size_t smem = 0;
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int nslots = convp_slots(p, &smem);
+    const int sms = ctx.sms;
+    const int nslots = ctx.conv_persistent ? convp_slots(p, &smem) : 0;
     if (nslots > 0 && p.ngroups <= sms) {
-      cudaError_t e = cudaFuncSetAttribute(tc_convp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-      if (e != cudaSuccess) return e;
       const int n_tiles = ceil_div(p.Lt, TC_TILE_M);
       int per_group = sms / p.ngroups;
       if (per_group > n_tiles * batch) per_group = n_tiles * batch;
-      if (const char* dbg = getenv("TTSB200_CONV_DEBUG")) p.debug = atoi(dbg);
-      p.trace = trace_begin(stream);
+      p.trace = trace_begin(ctx.trace_file, stream);
       const cudaError_t rc =
           launch_pdl(tc_convp_kernel, dim3(per_group * p.ngroups), dim3(NTP), smem, stream, p, nslots, n_tiles, batch);
-      trace_end(p.trace, 1000 + p.trace_id, stream);
+      trace_end(ctx.trace_file, p.trace, 1000 + p.trace_id, stream);
       return rc;
     }
-  }
-  {  // per-device attribute; cheap enough to set on every launch
-    cudaError_t e = cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-    if (e != cudaSuccess) return e;
   }
   const SmemPlan sp = smem_plan(p);
   if (sp.total > SMEM_MAX) return cudaErrorInvalidConfiguration;
   const dim3 grid(ceil_div(p.Lt, TC_TILE_M), p.ngroups, batch);
-  p.trace = trace_begin(stream);
+  p.trace = trace_begin(ctx.trace_file, stream);
   const cudaError_t rc = launch_pdl(tc_conv_kernel, grid, dim3(NT), sp.total, stream, p, sp.kb_stage, sp.nst);
-  trace_end(p.trace, 1000 + p.trace_id, stream);
+  trace_end(ctx.trace_file, p.trace, 1000 + p.trace_id, stream);
   return rc;
 }
 

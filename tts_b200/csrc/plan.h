@@ -70,6 +70,7 @@ struct ttsb200_plan {
   size_t pqmf_fact_off = 0;   // factorised-synthesis table (pqmf.cu), valid when pqmf_fact
   bool pqmf_fact = false;
   int hop_generator = 1;  // prod(upsample_factors)
+  ttsb::TcLaunchCtx ctx;  // device facts + debug knobs, read once at creation (nothing on the launch path calls getenv)
   ttsb::HostStaging host;
 };
 

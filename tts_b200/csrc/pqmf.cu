@@ -15,6 +15,8 @@
 #include <cmath>
 #include <cstdlib>
 
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace ttsb {
@@ -36,6 +38,47 @@ __device__ __forceinline__ float ld_after_wait(const float* p) {
   return v;
 }
 
+// 16 consecutive output samples of one thread -> global memory as full 32-byte sectors: two 32-byte stores of fp32,
+// or (fp16 waveform: TTSB200_OUT_F16, half the device->host bytes of the result) one 32-byte store of packed halves.
+__device__ __forceinline__ void store16(float* yt, const float (&acc)[4][4], int64_t t_first, int64_t Tout) {
+  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+      asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(yt + 8 * h), "f"(acc[2 * h][0]),
+                   "f"(acc[2 * h][1]), "f"(acc[2 * h][2]), "f"(acc[2 * h][3]), "f"(acc[2 * h + 1][0]),
+                   "f"(acc[2 * h + 1][1]), "f"(acc[2 * h + 1][2]), "f"(acc[2 * h + 1][3])
+                   : "memory");
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = acc[i][r];
+  }
+}
+__device__ __forceinline__ void store16(__half* yt, const float (&acc)[4][4], int64_t t_first, int64_t Tout) {
+  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __half2 lo = __floats2half2_rn(acc[i][0], acc[i][1]), hi = __floats2half2_rn(acc[i][2], acc[i][3]);
+      w[2 * i] = *reinterpret_cast<const uint32_t*>(&lo);
+      w[2 * i + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+    }
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(yt), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                 "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                 : "memory");
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = __float2half_rn(acc[i][r]);
+  }
+}
+__device__ __forceinline__ void store1(float* y, float v) { *y = v; }
+__device__ __forceinline__ void store1(__half* y, float v) { *y = __float2half_rn(v); }
+
 // ---- specialised N=4, K=63 (the only PQMF the reference instantiates: multiband_melgan_generator.py:24)
 constexpr int SQ_THREADS = 64;
 constexpr int SQ_QPT = 4;                        // q (groups of 4 outputs) per thread
@@ -44,9 +87,10 @@ constexpr int SQ_TILE = SQ_THREADS * SQ_QPT;     // 256 q per CTA -> 1024 output
 constexpr int SQ_HALO_L = 8;                     // window is q-7..q+8; 8 keeps float4 alignment
 constexpr int SQ_SMEM_Q = SQ_TILE + 16;          // 8 left + 8 right
 
+template <typename OutT>
 __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float* x,
                                                                       const float* __restrict__ G,
-                                                                      float* __restrict__ y, int Ts) {
+                                                                      OutT* __restrict__ y, int Ts) {
   __shared__ __align__(16) float sx[4][SQ_SMEM_Q];
   __shared__ __align__(16) float4 sc[4][16];              // sc[k][off+7] = 4*G[k][4*off+31-r], r=0..3
 
@@ -115,22 +159,8 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
   // each thread owns 4*QPT consecutive outputs, written as 32-byte stores (full sectors, no staging pass)
   const int64_t Tout = 4 * (int64_t)Ts;
   const int64_t t_first = (int64_t)(q0 + SQ_QPT * tid) * 4;
-  float* yt = y + (int64_t)b * Tout + t_first;
-  static_assert(SQ_QPT == 4, "the stores below write 16 floats per thread");
-  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-      asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(yt + 8 * h), "f"(acc[2 * h][0]),
-                   "f"(acc[2 * h][1]), "f"(acc[2 * h][2]), "f"(acc[2 * h][3]), "f"(acc[2 * h + 1][0]),
-                   "f"(acc[2 * h + 1][1]), "f"(acc[2 * h + 1][2]), "f"(acc[2 * h + 1][3])
-                   : "memory");
-  } else {
-#pragma unroll
-    for (int i = 0; i < SQ_QPT; ++i)
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = acc[i][r];
-  }
+  static_assert(SQ_QPT == 4, "store16 writes 16 samples per thread");
+  store16(y + (int64_t)b * Tout + t_first, acc, t_first, Tout);
 }
 
 // ---- factorised N=4, K=63 synthesis ------------------------------------------------------------------------
@@ -145,9 +175,10 @@ constexpr int SF_THREADS = 128;
 constexpr int SF_TILE = SF_THREADS * 4;          // 512 q per CTA -> 2048 output samples
 constexpr int SF_WIN = SF_TILE + 16;             // v window: q0-8 .. q0+TILE+7
 
+template <typename OutT>
 __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const float* x,
                                                                            const float* __restrict__ tbl,
-                                                                           float* __restrict__ y, int Ts) {
+                                                                           OutT* __restrict__ y, int Ts) {
   __shared__ __align__(16) float sv[8][SF_WIN];
   __shared__ __align__(16) float st[PQMF_FACT_TABLE];   // [p][k] modulation, then [p][8] FIR taps
 
@@ -220,26 +251,13 @@ __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const 
   const int64_t Tout = 4 * (int64_t)Ts;
   const int64_t t_first = (int64_t)(q0 + 4 * tid) * 4;
   if (t_first >= Tout) return;
-  float* yt = y + (int64_t)b * Tout + t_first;
-  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-      asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(yt + 8 * h), "f"(acc[2 * h][0]),
-                   "f"(acc[2 * h][1]), "f"(acc[2 * h][2]), "f"(acc[2 * h][3]), "f"(acc[2 * h + 1][0]),
-                   "f"(acc[2 * h + 1][1]), "f"(acc[2 * h + 1][2]), "f"(acc[2 * h + 1][3])
-                   : "memory");
-  } else {
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = acc[i][r];
-  }
+  store16(y + (int64_t)b * Tout + t_first, acc, t_first, Tout);
 }
 
 // ---- generic (any N, any taps): one thread per output sample ------------------------------------
+template <typename OutT>
 __global__ void pqmf_synth_generic_kernel(const float* __restrict__ x, const float* __restrict__ G,
-                                          float* __restrict__ y, int N, int K, int pad, int64_t Ts,
+                                          OutT* __restrict__ y, int N, int K, int pad, int64_t Ts,
                                           int64_t Tout) {
   const int b = blockIdx.y;
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -253,7 +271,18 @@ __global__ void pqmf_synth_generic_kernel(const float* __restrict__ x, const flo
     if (m < 0 || m >= Ts) continue;
     for (int k = 0; k < N; ++k) acc = fmaf(G[k * K + j], x[((int64_t)b * N + k) * Ts + m], acc);
   }
-  y[(int64_t)b * Tout + t] = acc * (float)N;
+  store1(y + (int64_t)b * Tout + t, acc * (float)N);
+}
+
+__global__ void f32_to_f16_kernel(const float* __restrict__ x, __half* __restrict__ y, int64_t n) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 4 <= n && ((reinterpret_cast<uintptr_t>(x + i) & 15) == 0) && ((reinterpret_cast<uintptr_t>(y + i) & 7) == 0)) {
+    const float4 v = *reinterpret_cast<const float4*>(x + i);
+    const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+    *reinterpret_cast<uint2*>(y + i) = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+  } else {
+    for (int64_t j = i; j < n && j < i + 4; ++j) y[j] = __float2half_rn(x[j]);
+  }
 }
 
 // analysis: y[b][k][m] = sum_j H[k][j] * x[b][N m + j - pad]   (zero outside)
@@ -314,38 +343,58 @@ bool pqmf_factor_4x63(const float* G, float* tbl) {
   return true;
 }
 
-cudaError_t pqmf_synthesis_fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, float* y,
-                                       cudaStream_t stream) {
-  if (batch <= 0 || Ts <= 0) return cudaSuccess;
-  static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_fact_kernel,
+namespace {
+template <typename OutT>
+cudaError_t fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, OutT* y, cudaStream_t stream) {
+  // shared-memory carve-out preference: a hint, set once per process (first device that launches)
+  static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_fact_kernel<OutT>,
                                                         cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   if (carve != cudaSuccess) return carve;
   const dim3 grid(ceil_div(Ts, SF_TILE), batch);
-  return launch_pdl(pqmf_synth_4x63_fact_kernel, grid, dim3(SF_THREADS), 0, stream, x, tbl, y, (int)Ts);
+  return launch_pdl(pqmf_synth_4x63_fact_kernel<OutT>, grid, dim3(SF_THREADS), 0, stream, x, tbl, y, (int)Ts);
 }
-// usable when whole float4s of every band are in or out of range and aligned
-bool pqmf_fact_usable(const float* x, int64_t Ts) {
-  if (getenv("TTSB200_PQMF_DIRECT")) return false;   // debug: force the direct kernel
-  return (Ts & 3) == 0 && Ts < (1 << 29) && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
-}
-
-cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int bands, int taps,
-                                  int64_t Ts, float* y, cudaStream_t stream) {
+template <typename OutT>
+cudaError_t direct_launch(const float* x, const float* G, int batch, int bands, int taps, int64_t Ts, OutT* y,
+                          cudaStream_t stream) {
   const int K = taps + 1, pad = taps / 2;
   const int64_t Tout = (int64_t)bands * Ts + 2 * pad - taps;
-  if (batch <= 0 || Ts <= 0 || Tout <= 0) return cudaSuccess;
   if (bands == 4 && taps == 62 && Ts < (1 << 30)) {
     const dim3 grid(ceil_div(Ts, SQ_TILE), batch);
     // 5.4 KB of static shared memory per 64-thread CTA: with the default carve-out only 21 CTAs fit an SM and cfg2's
     // 23.5 CTAs per SM spill into a second, nearly empty wave; ask for the full carve-out (32 CTAs per SM).
-    static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_kernel,
+    static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_kernel<OutT>,
                                                           cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (carve != cudaSuccess) return carve;
-    return launch_pdl(pqmf_synth_4x63_kernel, grid, dim3(SQ_THREADS), 0, stream, x, G, y, (int)Ts);
-  } else {
-    const dim3 grid(ceil_div(Tout, 256), batch);
-    pqmf_synth_generic_kernel<<<grid, 256, 0, stream>>>(x, G, y, bands, K, pad, Ts, Tout);
+    return launch_pdl(pqmf_synth_4x63_kernel<OutT>, grid, dim3(SQ_THREADS), 0, stream, x, G, y, (int)Ts);
   }
+  const dim3 grid(ceil_div(Tout, 256), batch);
+  pqmf_synth_generic_kernel<OutT><<<grid, 256, 0, stream>>>(x, G, y, bands, K, pad, Ts, Tout);
+  return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t pqmf_synthesis_fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, void* y, int out_f16,
+                                       cudaStream_t stream) {
+  if (batch <= 0 || Ts <= 0) return cudaSuccess;
+  return out_f16 ? fact_launch(x, tbl, batch, Ts, static_cast<__half*>(y), stream)
+                 : fact_launch(x, tbl, batch, Ts, static_cast<float*>(y), stream);
+}
+// usable when whole float4s of every band are in or out of range and aligned
+bool pqmf_fact_usable(const float* x, int64_t Ts) {
+  return (Ts & 3) == 0 && Ts < (1 << 29) && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+}
+
+cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int bands, int taps,
+                                  int64_t Ts, void* y, int out_f16, cudaStream_t stream) {
+  const int64_t Tout = (int64_t)bands * Ts + 2 * (taps / 2) - taps;
+  if (batch <= 0 || Ts <= 0 || Tout <= 0) return cudaSuccess;
+  return out_f16 ? direct_launch(x, G, batch, bands, taps, Ts, static_cast<__half*>(y), stream)
+                 : direct_launch(x, G, batch, bands, taps, Ts, static_cast<float*>(y), stream);
+}
+
+cudaError_t f32_to_f16_launch(const float* x, void* y, int64_t n, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  f32_to_f16_kernel<<<ceil_div(ceil_div(n, 4), 256), 256, 0, stream>>>(x, static_cast<__half*>(y), n);
   return cudaGetLastError();
 }
 

@@ -282,7 +282,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     p.trace_id = layer * 10 + trace_seq++ % 10;   // label for the debug timeline (trace.cuh)
     if (tc_conv_smem_bytes(p) > 224 * 1024)
       return fail(TTSB200_ERR_INVALID, std::string(name) + ": tile does not fit shared memory on the BF16 path");
-    TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, st); }));
+    TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, plan->ctx, st); }));
     return 0;
   };
   auto tap = [&](int layer, const __nv_bfloat16* x, int C, int64_t L, bool undo, int x_halo) -> int {
@@ -321,6 +321,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     const bool last_stage = s == S - 1;
     if (up_done) {
       up_done = false;   // the previous stage's stack already produced this stage's input in `cur`
+      if (int rc = tap(sp.layer_up, cur, C, L, nb == 0, cur_halo)) return rc;
     } else {
       TcConvParams p = base(sp.tc_up, Lin + 1);               // GEMM rows q = 0..Lin
       p.up_P = sp.P;
@@ -342,8 +343,12 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       if (int rc = tap(sp.layer_up, cur, C, L, nb == 0, cur_halo)) return rc;
     }
     const int half = (cfg.res_kernel - 1) / 2;
-    const bool fuse_head = last_stage && a->n_taps == 0 && head_fusable(plan);
-    const bool fuse_up = !last_stage && a->n_taps == 0 && up_fusable(plan, s);
+    // A tap of this stage's stack output needs that tensor in HBM, which the fused tails never write; every other
+    // tap (projection, transposed-conv outputs, head output) reads a tensor the fused schedule materialises anyway.
+    bool want_stack = false;
+    for (int i = 0; i < a->n_taps; ++i) want_stack |= a->tap_layers[i] == sp.layer_stack;
+    const bool fuse_head = last_stage && !want_stack && head_fusable(plan);
+    const bool fuse_up = !last_stage && !want_stack && up_fusable(plan, s);
     TcStackParams q = stack_tiling(plan, s, fuse_head, fuse_up);
     if (q.kt > 0) {  // whole ResidualStack in one kernel
       const CanonDims din = canon_dims(plan, C, L);
@@ -362,7 +367,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       double bytes = 2.0 * (2.0 * B * C * L + (double)(cfg.res_kernel + 2) * nb * C * C);
       if (fuse_head) {
         const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
-        q.head_out = to_out ? a->out : headf;
+        q.head_out = (to_out && a->out_dtype == TTSB200_OUT_F32) ? static_cast<float*>(a->out) : headf;
         macs += (double)cfg.proj_kernel * C * cfg.out_channels * L * B;
         bytes = 2.0 * B * C * L + 4.0 * B * cfg.out_channels * L;
         head_done = true;
@@ -378,7 +383,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         up_done = true;
       }
       TTSB_CUDA(ln.run(fuse_head ? "bf16.resstack.fused+head" : fuse_up ? "bf16.resstack.fused+convT" : "bf16.resstack.fused",
-                       sp.layer_stack, 2 * macs, bytes, [&] { return tc_stack_launch(q, B, st); }));
+                       sp.layer_stack, 2 * macs, bytes, [&] { return tc_stack_launch(q, B, plan->ctx, st); }));
       std::swap(cur, nxt);
     } else
     for (int bi = 0; bi < nb; ++bi) {
@@ -413,7 +418,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   {
     const int Cl = plan->stages.back().Cout;
     const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
-    float* dst = to_out ? a->out : headf;
+    float* dst = (to_out && a->out_dtype == TTSB200_OUT_F32) ? static_cast<float*>(a->out) : headf;
     const int ih = 4 + 3 * S;
     if (!head_done) {
       TcConvParams p = base(plan->tc_head, Lin);
@@ -424,14 +429,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         return rc;
     }
     if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
-    if (!to_out) {
-      const int N = cfg.pqmf_bands;
-      TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B, 8.0 * N * Lin * B, [&] {
-        if (plan->pqmf_fact && pqmf_fact_usable(headf, Lin))
-          return pqmf_synthesis_fact_launch(headf, Wf + plan->pqmf_fact_off, B, Lin, a->out, st);
-        return pqmf_synthesis_launch(headf, Wf + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, st);
-      }));
-    }
+    if (int rc = finish_output(plan, a, ln, dst, to_out, Lin)) return rc;
   }
   return 0;
 }

@@ -29,6 +29,7 @@
 // Tiles therefore advance as independent chains: the latency of one tile's epilogue (barrier -> tcgen05.ld ->
 // math -> tcgen05.st -> barrier) hides behind the MMAs and epilogues of the other tiles.
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -1012,11 +1013,17 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
 
 constexpr size_t SMEM_MAX = 227 * 1024 - 8 * 1024;   // static: barriers + bias tables (<= 4*2*192*4 B)
 
+// cudaFuncSetAttribute is per device and costs a driver call: done once per (instantiation, device).
 template <int CP, int KT, int CS, int TAIL>
-cudaError_t launch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
+cudaError_t launch(const TcStackParams& p, size_t smem, int grid, int device, cudaStream_t stream) {
   auto kern = tc_stack_kernel<CP, KT, CS, TAIL>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-  if (e != cudaSuccess) return e;
+  static std::atomic<uint64_t> attr_done{0};
+  const uint64_t bit = 1ull << (device & 63);
+  if (!(attr_done.load(std::memory_order_acquire) & bit)) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    if (e != cudaSuccess) return e;
+    attr_done.fetch_or(bit, std::memory_order_release);
+  }
   return launch_pdl(kern, dim3(grid), dim3(SERVICE_THREADS + KT * CS * 128), smem, stream, p);
 }
 
@@ -1107,7 +1114,7 @@ bool tc_stack_configure(TcStackParams& p) {
   return true;
 }
 
-cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream);
+cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, int device, cudaStream_t stream);
 
 size_t tc_stack_smem_bytes(const TcStackParams& p) {
   if (p.cp > 96) return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * RING_KB * p.cp * 2;
@@ -1116,7 +1123,7 @@ size_t tc_stack_smem_bytes(const TcStackParams& p) {
          (p.up_w && p.up_mode == 1 ? (size_t)2 * p.cp * p.up_n * 2 : 0);
 }
 
-cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t stream) {
+cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, const TcLaunchCtx& ctx, cudaStream_t stream) {
   TcStackParams p = p_in;
   if (p.kt != tc_stack_kt(p.cp) || p.kt == 0) return cudaErrorInvalidConfiguration;
   const size_t smem = tc_stack_smem_bytes(p);
@@ -1124,25 +1131,22 @@ cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, cudaStream_t s
   const int V = p.kt * 128 - 2 * (p.sum_d + (p.head_w ? (p.head_taps - 1) / 2 : p.up_w ? 1 : 0));
   p.batch = batch;
   p.n_chains = ceil_div(p.L + (p.up_w ? 1 : 0), V);   // the transposed conv also has GEMM row L
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int items = p.n_chains * batch;
-  const int slots = sms * tc_stack_ctas_per_sm(p.cp);
+  const int slots = ctx.sms * tc_stack_ctas_per_sm(p.cp);
   int grid = items < slots ? items : slots;
-  // test hook: few CTAs, so that each walks many items (item transitions, staging of the next item) on small inputs
-  if (const char* g = getenv("TTSB200_STACK_MAX_GRID")) grid = std::max(1, std::min(grid, atoi(g)));
-  if (const char* dbg = getenv("TTSB200_STACK_DEBUG")) p.debug = atoi(dbg);
-  p.trace = trace_begin(stream);
-  const cudaError_t rc = dispatch(p, smem, grid, stream);
-  trace_end(p.trace, p.cp, stream);
+  // test hook (read at plan creation): few CTAs, so that each walks many items on small inputs
+  if (ctx.stack_max_grid > 0) grid = std::max(1, std::min(grid, ctx.stack_max_grid));
+  p.debug = ctx.stack_debug;
+  p.trace = trace_begin(ctx.trace_file, stream);
+  const cudaError_t rc = dispatch(p, smem, grid, ctx.device, stream);
+  trace_end(ctx.trace_file, p.trace, p.cp, stream);
   return rc;
 }
 
-cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, cudaStream_t stream) {
+cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, int device, cudaStream_t stream) {
   const int tail = p.head_w ? 1 : p.up_w ? 2 : 0;
 #define TTSB_STACK_CASE(CP, KT, CS, TAIL) \
-  if (p.cp == CP && p.kt == KT && tail == TAIL) return launch<CP, KT, CS, TAIL>(p, smem, grid, stream)
+  if (p.cp == CP && p.kt == KT && tail == TAIL) return launch<CP, KT, CS, TAIL>(p, smem, grid, device, stream)
   TTSB_STACK_CASE(192, 1, 4, 0);
   TTSB_STACK_CASE(128, 1, 4, 0);
   TTSB_STACK_CASE(96, 2, 2, 0);

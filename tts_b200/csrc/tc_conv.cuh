@@ -7,6 +7,20 @@
 
 namespace ttsb {
 
+// Device facts and debug knobs of a plan, read ONCE at plan creation: nothing on the launch path queries the
+// driver or the environment (the streaming path, BASELINE config 5, is latency-bound).
+struct TcLaunchCtx {
+  int device = 0;
+  int sms = 148;
+  int stack_max_grid = 0;      // TTSB200_STACK_MAX_GRID: test hook, few CTAs so each walks many items
+  int stack_debug = 0;         // TTSB200_STACK_DEBUG / TTSB200_CONV_DEBUG: knock-out bits (trace builds only)
+  int conv_debug = 0;
+  int conv_persistent = 1;     // TTSB200_CONV_PERSISTENT=0: generic conv kernel everywhere
+  int pqmf_direct = 0;         // TTSB200_PQMF_DIRECT: direct 63-tap synthesis instead of the factorised form
+  const char* trace_file = nullptr;   // TTSB200_STACK_TRACE (trace builds only)
+};
+TcLaunchCtx tc_launch_ctx(int device);
+
 constexpr int TC_MAX_TAPS = 8;
 constexpr int TC_TILE_M = 128;   // GEMM rows (time positions) per CTA = UMMA M
 constexpr int TC_MAX_STAGES = 4; // weight ring depth
@@ -119,10 +133,10 @@ int tc_stack_kt(int cp);                          // 0: this channel count has n
 int tc_stack_cs(int cp);                          // epilogue warps per TMEM lane quarter (channel split)
 bool tc_stack_configure(TcStackParams& p);        // fills kt / sum_d / guard / w_sets from cp, dil[], nblocks
 size_t tc_stack_smem_bytes(const TcStackParams& p);
-cudaError_t tc_stack_launch(const TcStackParams& p, int batch, cudaStream_t stream);
+cudaError_t tc_stack_launch(const TcStackParams& p, int batch, const TcLaunchCtx& ctx, cudaStream_t stream);
 
 size_t tc_conv_smem_bytes(const TcConvParams& p);
-cudaError_t tc_conv_launch(const TcConvParams& p, int batch, cudaStream_t stream);
+cudaError_t tc_conv_launch(const TcConvParams& p, int batch, const TcLaunchCtx& ctx, cudaStream_t stream);
 
 // mel fp32 [B][C][T] -> canonical bf16 with replicate padding `pad` folded in and reflect margins
 cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out,

@@ -35,20 +35,20 @@ __device__ __forceinline__ Tracer make_tracer(long long*, int, bool) { return Tr
 constexpr int TRACE_ROLES = 40;
 
 // Host side: allocate before the launch, dump + free after it.
-inline long long* trace_begin(cudaStream_t stream) {
-  if (!getenv("TTSB200_STACK_TRACE")) return nullptr;
+inline long long* trace_begin(const char* file, cudaStream_t stream) {
+  if (!file) return nullptr;
   long long* d = nullptr;
   cudaMalloc(&d, TRACE_ROLES * 256 * sizeof(long long));
   cudaMemsetAsync(d, 0, TRACE_ROLES * 256 * sizeof(long long), stream);
   return d;
 }
-inline void trace_end(long long* d, int id, cudaStream_t stream) {
+inline void trace_end(const char* file, long long* d, int id, cudaStream_t stream) {
   if (!d) return;
   std::vector<long long> h(TRACE_ROLES * 256);
   cudaStreamSynchronize(stream);
   cudaMemcpy(h.data(), d, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
   cudaFree(d);
-  if (FILE* f = fopen(getenv("TTSB200_STACK_TRACE"), "a")) {
+  if (FILE* f = fopen(file, "a")) {
     for (int r = 0; r < TRACE_ROLES; ++r)
       for (int i = 0; i < 256 && h[r * 256 + i]; i += 2)
         fprintf(f, "%d %d %d %lld\n", id, r, (int)h[r * 256 + i], h[r * 256 + i + 1]);

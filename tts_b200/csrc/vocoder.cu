@@ -168,6 +168,31 @@ int copy_tap(const ttsb200_forward_args* a, int layer, const float* src, int C, 
   return 0;
 }
 
+// Last step of both schedules: `sub` holds the head output [B][out_channels][Lin] (fp32).  Either it already is the
+// result (no PQMF / skip_pqmf, fp32 out), or it is converted to fp16, or PQMF synthesis turns it into the waveform
+// (the synthesis kernels store fp32 or fp16 themselves).
+int finish_output(const ttsb200_plan* plan, const ttsb200_forward_args* a, Launcher& ln, const float* sub, bool to_out,
+                  int64_t Lin) {
+  const ttsb200_generator_config& cfg = plan->cfg;
+  const int B = a->batch;
+  const int f16 = a->out_dtype == TTSB200_OUT_F16;
+  cudaStream_t st = static_cast<cudaStream_t>(a->stream);
+  if (to_out) {
+    if (f16) {
+      const int64_t n = (int64_t)B * cfg.out_channels * Lin;
+      TTSB_CUDA(ln.run("out.f32_to_f16", -1, 0.0, 6.0 * n, [&] { return f32_to_f16_launch(sub, a->out, n, st); }));
+    }
+    return 0;
+  }
+  const int N = cfg.pqmf_bands;
+  TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B, (f16 ? 6.0 : 8.0) * N * Lin * B, [&] {
+    if (plan->pqmf_fact && !plan->ctx.pqmf_direct && pqmf_fact_usable(sub, Lin))
+      return pqmf_synthesis_fact_launch(sub, plan->blob + plan->pqmf_fact_off, B, Lin, a->out, f16, st);
+    return pqmf_synthesis_launch(sub, plan->blob + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, f16, st);
+  }));
+  return 0;
+}
+
 // fp32 schedule: 1 + S*(1 + 2n) + 1 (+1 PQMF) launches, every intermediate NCL fp32 in `workspace`.
 int forward_f32(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   const ttsb200_generator_config& cfg = plan->cfg;
@@ -253,7 +278,8 @@ int forward_f32(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   {  // LeakyReLU + ReflectionPad1d + Conv1d k7 + Tanh
     const int Cl = plan->head.Cin;
     const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
-    float* dst = to_out ? a->out : spare0;
+    const bool f16 = a->out_dtype == TTSB200_OUT_F16;
+    float* dst = (to_out && !f16) ? static_cast<float*>(a->out) : spare0;
     ConvParams p = base_params(plan->head, dst, Lin, Lin);
     p.src[0] = make_src(cur, W + plan->head.w_off, Cl, Lin, cfg.proj_kernel, 1, -pp, false, true);
     p.tanh_out = 1;
@@ -264,14 +290,7 @@ int forward_f32(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
                               (double)cfg.proj_kernel * Cl * cfg.out_channels),
                      [&] { return conv_f32_launch(p, B, plan->head.cpt, st); }));
     if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
-    if (!to_out) {
-      const int N = cfg.pqmf_bands;
-      TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B, 8.0 * N * Lin * B, [&] {
-        if (plan->pqmf_fact && pqmf_fact_usable(spare0, Lin))
-          return pqmf_synthesis_fact_launch(spare0, W + plan->pqmf_fact_off, B, Lin, a->out, st);
-        return pqmf_synthesis_launch(spare0, W + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, st);
-      }));
-    }
+    if (int rc = finish_output(plan, a, ln, dst, to_out, Lin)) return rc;
   }
   return 0;
 }
@@ -381,6 +400,7 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
   int prev = 0;
   cudaGetDevice(&prev);
   cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) plan->ctx = tc_launch_ctx(device);
   if (e == cudaSuccess) e = cudaMalloc(&plan->blob, plan->blob_floats * sizeof(float));
   if (e == cudaSuccess)
     e = cudaMemcpy(plan->blob, bb.data.data(), plan->blob_floats * sizeof(float), cudaMemcpyHostToDevice);
@@ -463,6 +483,17 @@ int32_t ttsb200_generator_forward(const ttsb200_plan* plan, const ttsb200_forwar
   for (const StagePlan& sp : plan->stages) fmax = std::max(fmax, sp.f);
   if ((int64_t)a->batch * fmax > 65535)
     return fail(TTSB200_ERR_INVALID, "batch too large for one launch (batch * max upsample factor > 65535); split the batch");
+  if (a->out_dtype != TTSB200_OUT_F32 && a->out_dtype != TTSB200_OUT_F16)
+    return fail(TTSB200_ERR_INVALID, "unknown out_dtype");
+  // The caller's current device need not be the plan's (a generator on cuda:1 called while cuda:0 is current,
+  // which the reference supports): launches, attribute calls and events all go to plan->device.
+  int prev = 0;
+  TTSB_CUDA(cudaGetDevice(&prev));
+  if (prev != plan->device) TTSB_CUDA(cudaSetDevice(plan->device));
+  struct Restore {
+    int prev, cur;
+    ~Restore() { if (prev != cur) cudaSetDevice(prev); }
+  } restore{prev, plan->device};
   switch (a->precision) {
     case TTSB200_F32: return forward_f32(plan, a);
     case TTSB200_BF16: return forward_bf16(plan, a);
@@ -486,7 +517,9 @@ int32_t ttsb200_generator_forward_host(ttsb200_plan* plan, const float* mel_host
   if (!h.stream) TTSB_CUDA(cudaStreamCreateWithFlags(&h.stream, cudaStreamNonBlocking));
   const size_t in_b = (size_t)batch * plan->cfg.in_channels * frames * sizeof(float);
   const int64_t out_len = ttsb200_output_length(plan, frames, pad, 0);
-  const size_t out_b = (size_t)batch * (size_t)out_len * sizeof(float);
+  // [batch, 1, samples] with PQMF synthesis, [batch, out_channels, samples] without (MelganGenerator(out_channels=4))
+  const size_t out_ch = plan->cfg.pqmf_bands > 0 ? 1 : (size_t)plan->cfg.out_channels;
+  const size_t out_b = (size_t)batch * out_ch * (size_t)out_len * sizeof(float);
   const int64_t ws = ttsb200_workspace_bytes(plan, batch, frames, pad, precision);
   if (ws < 0) return (int32_t)ws;
   auto ensure = [](void** p, size_t* have, size_t need) -> cudaError_t {
@@ -516,7 +549,7 @@ int32_t ttsb200_pqmf_synthesis(const float* x, const float* G, int32_t batch, in
   if (!x || !G || !y) return fail(TTSB200_ERR_INVALID, "NULL argument");
   if (batch <= 0 || bands <= 0 || taps <= 0 || Ts <= 0 || batch > 65535)
     return fail(TTSB200_ERR_INVALID, "batch/bands/taps/Ts out of range");
-  TTSB_CUDA(pqmf_synthesis_launch(x, G, batch, bands, taps, Ts, y, static_cast<cudaStream_t>(stream)));
+  TTSB_CUDA(pqmf_synthesis_launch(x, G, batch, bands, taps, Ts, y, 0, static_cast<cudaStream_t>(stream)));
   return 0;
 }
 

@@ -1,6 +1,7 @@
 """GeneratorEngine: owns one ttsb200_plan (device-resident, kernel-ready weights) and launches
 generator.inference() through the C ABI.  PyTorch is used only for device memory and streams.
 """
+import collections
 import ctypes
 import threading
 
@@ -97,7 +98,7 @@ class GeneratorEngine:
         _lib.check(lib.ttsb200_plan_create(ctypes.byref(cfg), ptrs, len(tensors), index, ctypes.byref(self._h)))
         self.cfg = cfg
         self.index = index
-        self._ws = {}
+        self._ws = collections.OrderedDict()
         self._lock = threading.Lock()
 
     # ---- shape helpers
@@ -115,21 +116,34 @@ class GeneratorEngine:
     def launch_count(self, precision=_lib.F32, skip_pqmf=False):
         return _lib.check(_lib.load().ttsb200_launch_count(self._h, precision, int(skip_pqmf)))
 
+    MAX_WORKSPACES = 8
+
     def _workspace(self, nbytes, stream_key):
-        # one scratch tensor per (thread, stream): Flask threads share a module (server.py:64,82)
-        key = (threading.get_ident(), stream_key)
+        """Scratch for one forward, keyed by the launch stream and nothing else: work on one stream is serialised
+        by the stream, so the Flask request threads that share a module (TTS/server/server.py:64,82) and all launch
+        on the default stream share ONE workspace instead of leaking one per thread.  At most MAX_WORKSPACES are
+        kept (least recently used first out); an evicted tensor goes back to torch's caching allocator, which only
+        reuses the block in stream order of the stream it was allocated on — the stream that may still be running
+        kernels on it — so eviction is safe while work is in flight."""
         with self._lock:
-            ws = self._ws.get(key)
+            ws = self._ws.get(stream_key)
             if ws is None or ws.numel() < nbytes:
                 ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
-                self._ws[key] = ws
+                self._ws[stream_key] = ws
+            self._ws.move_to_end(stream_key)
+            while len(self._ws) > self.MAX_WORKSPACES:
+                self._ws.popitem(last=False)
         return ws
 
     # ---- the hot call
-    def forward(self, mel, pad, precision=_lib.F32, skip_pqmf=False, tap_layers=None, profile=None, out=None):
-        """mel: CUDA fp32 [B, in_channels, T] on this engine's device. Returns [B, C_out, samples]."""
+    def forward(self, mel, pad, precision=_lib.F32, skip_pqmf=False, tap_layers=None, profile=None, out=None,
+                out_dtype=None):
+        """mel: CUDA fp32 [B, in_channels, T] on this engine's device. Returns [B, C_out, samples] (fp32, or fp16
+        with ``out_dtype=torch.float16`` / an fp16 ``out``)."""
         if mel.dim() != 3 or mel.shape[1] != self.cfg.in_channels:
             raise RuntimeError(f"expected mel of shape [B, {self.cfg.in_channels}, T], got {tuple(mel.shape)}")
+        if mel.device != self.device:
+            raise RuntimeError(f"mel is on {mel.device}, the plan on {self.device}")
         mel = mel.contiguous()
         B, _, T = mel.shape
         if B == 0 or T == 0:
@@ -137,8 +151,21 @@ class GeneratorEngine:
         lib = _lib.load()
         n_out = self.output_length(T, pad, skip_pqmf)
         ch = 1 if (self.cfg.pqmf_bands and not skip_pqmf) else self.cfg.out_channels
+        if out is not None:
+            out_dtype = out.dtype
+            if tuple(out.shape) != (B, ch, n_out) or not out.is_contiguous() or out.device != self.device:
+                raise RuntimeError(f"out must be a contiguous {(B, ch, n_out)} tensor on {self.device}")
+        out_dtype = out_dtype or torch.float32
+        if out_dtype not in (torch.float32, torch.float16):
+            raise RuntimeError("out dtype must be torch.float32 or torch.float16")
+        # The module may live on a device that is not the caller's current one (the reference supports that):
+        # allocate and look the stream up under the plan's device; the C entry point switches devices itself.
+        with torch.cuda.device(self.device):
+            return self._forward(lib, mel, B, T, pad, precision, skip_pqmf, tap_layers, profile, out, out_dtype, ch, n_out)
+
+    def _forward(self, lib, mel, B, T, pad, precision, skip_pqmf, tap_layers, profile, out, out_dtype, ch, n_out):
         if out is None:
-            out = torch.empty((B, ch, n_out), dtype=torch.float32, device=self.device)
+            out = torch.empty((B, ch, n_out), dtype=out_dtype, device=self.device)
         stream = torch.cuda.current_stream(self.device)
         ws_bytes = self.workspace_bytes(B, T, pad, precision)
         ws = self._workspace(ws_bytes, stream.cuda_stream)
@@ -149,6 +176,7 @@ class GeneratorEngine:
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         a.stream = stream.cuda_stream
         a.skip_pqmf = int(skip_pqmf)
+        a.out_dtype = _lib.OUT_F16 if out_dtype == torch.float16 else _lib.OUT_F32
         taps = {}
         if tap_layers:
             ids = (ctypes.c_int32 * len(tap_layers))(*tap_layers)
@@ -180,7 +208,7 @@ class GeneratorEngine:
         if getattr(self, "_h", None):
             _lib.load().ttsb200_plan_destroy(self._h)
             self._h = ctypes.c_void_p()
-            self._ws = {}
+            self._ws = collections.OrderedDict()
 
     def __del__(self):
         try:

@@ -60,14 +60,10 @@ def hop_length(generator):
     return hop * (pq.N if pq is not None else 1)
 
 
-def _infer_unpadded(generator, mel):
-    """generator.inference with inference_padding forced to 0 for this call (the attribute is restored)."""
-    saved = generator.inference_padding
-    generator.inference_padding = 0
-    try:
-        return generator.inference(mel)
-    finally:
-        generator.inference_padding = saved
+def _infer_unpadded(generator, mel, out=None):
+    """generator.inference with padding 0 for this call only; the shared module's attribute is never written
+    (request threads may be running inference() on the same module, TTS/server/server.py:64,82)."""
+    return generator.inference_padded(mel, 0, out=out)
 
 
 def local_slice(generator, mel_padded, start, end, halo, infer_fn=None):

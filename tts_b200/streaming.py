@@ -24,38 +24,46 @@ class GraphedInference:
     cost more host time than the kernels take on the device.  Every steady-state window has the same shape, so the
     whole forward — the C-ABI launches included, they go to the capturing stream like any other launch — is captured
     once per shape and replayed; the first chunks of a stream and the flush have their own (also cached) shapes.
-    The result is copied out of the graph's static buffer, so callers may keep it."""
+    The result is copied out of the graph's static buffer, so callers may keep it.
+
+    A captured graph holds raw pointers into the engine's plan (weight blobs) and workspace.  ``load_state_dict``,
+    ``remove_weight_norm`` or ``.to()`` make the generator build a NEW engine and free the old plan, so every
+    graph is tied to the engine it was captured from: each entry keeps a reference to that engine (its plan and
+    workspace stay alive as long as the graph does) and the whole cache is dropped when the generator's current
+    engine is a different object."""
 
     def __init__(self, generator, max_graphs=8):
         self.g = generator
         self.max_graphs = max_graphs
         self._graphs = {}
+        self._engine = None      # the engine every cached graph was captured from
 
     def _capture(self, shape, device):
         static_in = torch.zeros(shape, dtype=torch.float32, device=device)
-        saved = self.g.inference_padding
-        self.g.inference_padding = 0
-        try:
-            side = torch.cuda.Stream(device)
-            side.wait_stream(torch.cuda.current_stream(device))
-            with torch.cuda.stream(side):          # warm-up off the capture: plan creation, attribute calls, workspace
-                self.g.inference(static_in)
-            torch.cuda.current_stream(device).wait_stream(side)
-            torch.cuda.synchronize(device)
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                static_out = self.g.inference(static_in)
-        finally:
-            self.g.inference_padding = saved
+        side = torch.cuda.Stream(device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        with torch.cuda.stream(side):          # warm-up off the capture: plan creation, attribute calls, workspace
+            self.g.inference_padded(static_in, 0)
+        torch.cuda.current_stream(device).wait_stream(side)
+        torch.cuda.synchronize(device)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            static_out = self.g.inference_padded(static_in, 0)
         return graph, static_in, static_out
 
     def __call__(self, mel):
+        engine = self.g._get_engine()          # rebuilt when the weights / device changed
+        if engine is not self._engine:
+            self._graphs.clear()               # graphs of a replaced engine point at freed weights: never replay them
+            self._engine = engine
         key = (tuple(mel.shape), mel.device)
         entry = self._graphs.get(key)
         if entry is None:
             if len(self._graphs) >= self.max_graphs:
                 self._graphs.pop(next(iter(self._graphs)))
             entry = self._graphs[key] = self._capture(tuple(mel.shape), mel.device)
+            if self.g._get_engine() is not engine:   # the capture itself must not have swapped engines
+                raise RuntimeError("GraphedInference: generator weights changed during graph capture")
         graph, static_in, static_out = entry
         static_in.copy_(mel, non_blocking=True)
         graph.replay()
@@ -87,12 +95,7 @@ class StreamingVocoder:
         self.emitted = 0       # frames of the padded stream already turned into samples
 
     def _infer_unpadded(self, mel):
-        saved = self.g.inference_padding
-        self.g.inference_padding = 0
-        try:
-            return self.g.inference(mel)
-        finally:
-            self.g.inference_padding = saved
+        return self.g.inference_padded(mel, 0)   # never touches the shared module's inference_padding
 
     def _window(self, start, end, total_known, final):
         """Samples of padded-stream frames [start, end)."""

@@ -81,8 +81,9 @@ class MelganGenerator(nn.Module):
         with self._engine_lock:
             if self._engine is None or self._engine_sig != sig:
                 from ...engine import GeneratorEngine
-                if self._engine is not None:
-                    self._engine.close()
+                # The old engine is released, not closed: another thread may be inside its forward(), and CUDA
+                # graphs captured from it (tts_b200/streaming.py) hold a reference.  Its plan is destroyed when the
+                # last reference goes (GeneratorEngine.__del__; cudaFree waits for in-flight work).
                 self._engine = GeneratorEngine(self, dev)
                 self._engine_sig = sig
         return self._engine
@@ -97,11 +98,20 @@ class MelganGenerator(nn.Module):
         self._frozen = False
         return super()._apply(fn, *a, **kw)
 
-    def _run(self, c, pad, skip_pqmf, tap_layers=None, profile=None):
+    _SKIP_PQMF = True   # MultibandMelganGenerator.inference appends PQMF synthesis (multiband_melgan_generator.py:38)
+
+    def _run(self, c, pad, skip_pqmf, tap_layers=None, profile=None, out=None, out_dtype=None):
         eng = self._get_engine()
         c = c.detach().to(device=eng.device, dtype=torch.float32, non_blocking=True)   # async when c is pinned
         prec = _lib.PRECISIONS[self.precision]
-        return eng.forward(c, int(pad), prec, skip_pqmf=skip_pqmf, tap_layers=tap_layers, profile=profile)
+        return eng.forward(c, int(pad), prec, skip_pqmf=skip_pqmf, tap_layers=tap_layers, profile=profile, out=out,
+                           out_dtype=out_dtype)
+
+    def inference_padded(self, c, pad, out=None):
+        """``inference`` with an explicit padding for this call only.  Long-form and streaming windows run with
+        padding 0 (tts_b200/longform.py, streaming.py); they must not change ``inference_padding`` on a module
+        that request threads share (TTS/server/server.py:64,82)."""
+        return self._run(c, int(pad), self._SKIP_PQMF, out=out)
 
     # ------------------------------------------------------------------ reference surface
     def forward(self, c):
@@ -112,13 +122,17 @@ class MelganGenerator(nn.Module):
     def inference(self, c):
         return self._run(c, self.inference_padding, True)
 
-    def inference_to_host(self, c, out=None):
+    def inference_to_host(self, c, out=None, dtype=torch.float32):
         """inference() followed by an asynchronous device->host copy into pinned memory, all on the current
         stream, so the caller's ``.cpu().numpy()`` sync disappears (TTS/server/synthesizer.py:155-159,
         SURVEY.md §8f-2).  Returns ``(wav_host, event)``: ``wav_host`` (pinned, reusable via ``out=``) is valid
         once ``event.synchronize()`` returns.  With a pinned ``c`` the upload is asynchronous too, so calls on
-        alternating streams overlap copies with compute."""
-        y = self.inference(c)
+        alternating streams overlap copies with compute.
+
+        ``dtype=torch.float16`` makes the last kernel store the waveform as fp16 (|wav| <= 1 after tanh / PQMF, so
+        the rounding is <= 2^-11 relative, well inside the 16-bit WAV every reference caller ends in,
+        TTS/utils/audio.py:338-340) and halves the device->host bytes."""
+        y = self._run(c, self.inference_padding, self._SKIP_PQMF, out_dtype=dtype)
         if out is None:
             out = torch.empty(y.shape, dtype=y.dtype, pin_memory=True)
         out.copy_(y, non_blocking=True)
@@ -126,9 +140,9 @@ class MelganGenerator(nn.Module):
         ev.record(torch.cuda.current_stream(y.device))
         return out, ev
 
-    def inference_with_taps(self, c, tap_layers):
+    def inference_with_taps(self, c, tap_layers, profile=None):
         """inference() that also returns {layers[i] index: output} for per-layer parity tests."""
-        return self._run(c, self.inference_padding, True, tap_layers=list(tap_layers))
+        return self._run(c, self.inference_padding, self._SKIP_PQMF, tap_layers=list(tap_layers), profile=profile)
 
     def remove_weight_norm(self):
         for m in self.modules():

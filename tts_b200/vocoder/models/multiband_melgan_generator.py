@@ -6,6 +6,8 @@ from ..layers.pqmf import PQMF
 
 
 class MultibandMelganGenerator(MelganGenerator):
+    _SKIP_PQMF = False
+
     def __init__(self,
                  in_channels=80,
                  out_channels=4,
@@ -29,6 +31,3 @@ class MultibandMelganGenerator(MelganGenerator):
     def inference(self, cond_features):
         # sub-band generator and PQMF synthesis run inside one plan launch sequence
         return self._run(cond_features, self.inference_padding, False)
-
-    def inference_with_taps(self, c, tap_layers):
-        return self._run(c, self.inference_padding, False, tap_layers=list(tap_layers))

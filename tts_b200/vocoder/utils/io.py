@@ -1,4 +1,5 @@
-"""Checkpoint I/O for the vocoder generators — mirrors TTS/vocoder/utils/io.py:9-18 (load) and :21-46 (save).
+"""Checkpoint loading for the vocoder generators — mirrors TTS/vocoder/utils/io.py:9-18 (``load_checkpoint``).
+Writing checkpoints is the trainer's job and out of scope (the format is consumed, not rebuilt).
 
 A reference checkpoint is a ``torch.save``d dict whose ``'model'`` entry is the generator's state dict, in the
 weight-norm form the trainer writes (``layers.N.weight_g`` / ``weight_v``; ``pqmf_layer.H/G/updown_filter``
@@ -10,8 +11,6 @@ Checkpoints pickled when the toolkit was called ``mozilla_voice_tts`` refer to m
 reference retries with an unpickler that renames them (TTS/utils/io.py:6-9).  Same behaviour here, with the
 name mapped onto this package when the TTS package itself is not importable.
 """
-import datetime
-import os
 import pickle
 
 import torch
@@ -42,52 +41,25 @@ class _RenamingPickle:
     HIGHEST_PROTOCOL = pickle.HIGHEST_PROTOCOL
 
 
-def load_checkpoint(model, checkpoint_path, use_cuda=False):
-    """(model, state) with ``state['model']`` loaded strictly; same signature as the reference's."""
+def load_checkpoint(model, checkpoint_path, use_cuda=False, allow_pickle=True):
+    """(model, state) with ``state['model']`` loaded strictly; same signature as the reference's.
+
+    A vocoder checkpoint is a plain dict of tensors and scalars, so the safe loader (``weights_only=True``) is
+    tried first.  Trainer checkpoints that pickled optimizer / scheduler objects, or that were written under the
+    toolkit's old package name, need the unrestricted unpickler the reference always uses
+    (TTS/vocoder/utils/io.py:10-15) — which executes code from the file; pass ``allow_pickle=False`` to refuse
+    that for files of unknown origin."""
+    cpu = torch.device("cpu")
     try:
-        state = torch.load(checkpoint_path, map_location=torch.device("cpu"), weights_only=False)
-    except ModuleNotFoundError:
-        state = torch.load(checkpoint_path, map_location=torch.device("cpu"), pickle_module=_RenamingPickle,
-                           weights_only=False)
+        state = torch.load(checkpoint_path, map_location=cpu, weights_only=True)
+    except Exception:
+        if not allow_pickle:
+            raise
+        try:
+            state = torch.load(checkpoint_path, map_location=cpu, weights_only=False)
+        except ModuleNotFoundError:
+            state = torch.load(checkpoint_path, map_location=cpu, pickle_module=_RenamingPickle, weights_only=False)
     model.load_state_dict(state["model"])
     if use_cuda:
         model.cuda()
     return model, state
-
-
-def save_model(model, optimizer, scheduler, model_disc, optimizer_disc, scheduler_disc, current_step, epoch,
-               output_path, **kwargs):
-    def sd(m):
-        return m.state_dict() if m is not None else None
-    state = {
-        "model": sd(model),
-        "optimizer": sd(optimizer),
-        "scheduler": sd(scheduler),
-        "model_disc": sd(model_disc),
-        "optimizer_disc": sd(optimizer_disc),
-        "scheduler_disc": sd(scheduler_disc),
-        "step": current_step,
-        "epoch": epoch,
-        "date": datetime.date.today().strftime("%B %d, %Y"),
-    }
-    state.update(kwargs)
-    torch.save(state, output_path)
-
-
-def save_checkpoint(model, optimizer, scheduler, model_disc, optimizer_disc, scheduler_disc, current_step, epoch,
-                    output_folder, **kwargs):
-    checkpoint_path = os.path.join(output_folder, "checkpoint_{}.pth.tar".format(current_step))
-    print(" > CHECKPOINT : {}".format(checkpoint_path))
-    save_model(model, optimizer, scheduler, model_disc, optimizer_disc, scheduler_disc, current_step, epoch,
-               checkpoint_path, **kwargs)
-
-
-def save_best_model(target_loss, best_loss, model, optimizer, scheduler, model_disc, optimizer_disc, scheduler_disc,
-                    current_step, epoch, output_folder, **kwargs):
-    if target_loss < best_loss:
-        checkpoint_path = os.path.join(output_folder, "best_model.pth.tar")
-        print(" > BEST MODEL : {}".format(checkpoint_path))
-        save_model(model, optimizer, scheduler, model_disc, optimizer_disc, scheduler_disc, current_step, epoch,
-                   checkpoint_path, model_loss=target_loss, **kwargs)
-        best_loss = target_loss
-    return best_loss
