@@ -95,6 +95,15 @@ typedef struct ttsb200_forward_args {
   float* const* tap_out;    /*   each device [batch, C_i, L_i] fp32                              */
   ttsb200_profile* profile; /* optional                                                          */
   int32_t out_dtype;        /* ttsb200_out_dtype of `out` (taps are always fp32)                 */
+  /* Optional output window (all zero = the whole result, densely packed): only samples             */
+  /* [out_keep_lo, out_keep_lo + out_keep_len) of every row are stored, row b starting at           */
+  /* out + b * out_batch_stride elements.  A long-form rank or a streaming window computes halo     */
+  /* samples it must not emit; with a window its last kernel stores the kept samples straight into  */
+  /* their place in the final buffer — which may be a peer GPU's memory mapped over NVLink — and     */
+  /* nothing is gathered or concatenated afterwards (tts_b200/longform.py).                         */
+  int64_t out_keep_lo;
+  int64_t out_keep_len;
+  int64_t out_batch_stride;
 } ttsb200_forward_args;
 
 TTSB200_API int32_t ttsb200_abi_version(void);
@@ -169,6 +178,13 @@ TTSB200_API int32_t ttsb200_profile_read(ttsb200_profile* profile, ttsb200_launc
 
 /* Number of kernels one ttsb200_generator_forward() launches for this shape (bench "gpu_launches"). */
 TTSB200_API int32_t ttsb200_launch_count(const ttsb200_plan* plan, int32_t precision, int32_t skip_pqmf);
+
+/* Diagnostics for the roofline denominators MEASURED_PEAKS.json does not carry (bench.py).
+ * fp32 FFMA rate of `device` in TFLOP/s (register-resident FMA loop on every SM, CUDA events) — the ceiling of the
+ * TTSB200_F32 path; pinned host<->device copy rate in GB/s over `streams` concurrent copies of `bytes` each
+ * (direction 0 = host to device, 1 = device to host) — the ceiling of the end-to-end figure.  Negative on error. */
+TTSB200_API double ttsb200_diag_ffma_tflops(int32_t device);
+TTSB200_API double ttsb200_diag_hostlink_gbs(int32_t device, int32_t direction, int64_t bytes, int32_t streams);
 
 #ifdef __cplusplus
 }

@@ -80,7 +80,7 @@ __global__ void latency_kernel(long long* out, uint32_t* sink) {
   __shared__ uint64_t bar;
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
-    mbar_init(&bar, 32);
+    mbar_init(&bar, blockDim.x);
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc(&tmem_base, 128);
@@ -177,6 +177,7 @@ __global__ void roundtrip_kernel(int rounds, int nmma, int ts, long long* out) {
 }
 
 int main() {
+  setvbuf(stdout, NULL, _IOLBF, 0);
   long long* dC;
   uint32_t* dS;
   cudaMalloc(&dC, 8 * 1024);

@@ -35,17 +35,17 @@ def test_struct_layout_matches_header(tmp_path):
     src = tmp_path / "sz.c"
     src.write_text(
         '#include <stdio.h>\n#include <stddef.h>\n#include "tts_b200.h"\n'
-        'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(ttsb200_generator_config),'
+        'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(ttsb200_generator_config),'
         'sizeof(ttsb200_forward_args), sizeof(ttsb200_launch_record), offsetof(ttsb200_forward_args, out),'
         'offsetof(ttsb200_forward_args, tap_layers), offsetof(ttsb200_forward_args, profile),'
-        'offsetof(ttsb200_forward_args, out_dtype));return 0;}\n')
+        'offsetof(ttsb200_forward_args, out_dtype), offsetof(ttsb200_forward_args, out_batch_stride));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
                            str(src), "-o", str(exe)])
     got = [int(v) for v in subprocess.check_output([str(exe)]).split()]
     F = _lib.ForwardArgs
     assert got == [ctypes.sizeof(_lib.GeneratorConfig), ctypes.sizeof(F), ctypes.sizeof(_lib.LaunchRecord),
-                   F.out.offset, F.tap_layers.offset, F.profile.offset, F.out_dtype.offset]
+                   F.out.offset, F.tap_layers.offset, F.profile.offset, F.out_dtype.offset, F.out_batch_stride.offset]
 
 
 def test_argument_validation_without_gpu():

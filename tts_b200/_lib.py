@@ -48,6 +48,9 @@ class ForwardArgs(ctypes.Structure):
         ("tap_out", ctypes.POINTER(ctypes.c_void_p)),
         ("profile", ctypes.c_void_p),
         ("out_dtype", ctypes.c_int32),
+        ("out_keep_lo", ctypes.c_int64),
+        ("out_keep_len", ctypes.c_int64),
+        ("out_batch_stride", ctypes.c_int64),
     ]
 
 
@@ -89,6 +92,8 @@ SYMBOLS = {
     "ttsb200_profile_reset": (None, [ctypes.c_void_p]),
     "ttsb200_profile_read": (ctypes.c_int32, [ctypes.c_void_p, ctypes.POINTER(LaunchRecord), ctypes.c_int32]),
     "ttsb200_launch_count": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32]),
+    "ttsb200_diag_ffma_tflops": (ctypes.c_double, [ctypes.c_int32]),
+    "ttsb200_diag_hostlink_gbs": (ctypes.c_double, [ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32]),
 }
 
 _lib = None

@@ -93,9 +93,14 @@ int conv_f32_pick_cpt(int Cout);
 cudaError_t conv_f32_launch(const ConvParams& p, int batch, int cpt, cudaStream_t stream);
 
 // ---- PQMF (pqmf.cu) ----------------------------------------------------------------------------
-// y: fp32, or fp16 when out_f16 (ttsb200_out_dtype)
+// y: fp32, or fp16 when out_f16 (ttsb200_out_dtype).  crop (optional): only samples [lo, lo + len) of every row are
+// stored, row b at y + b * batch_stride (elements) — the kept range of a long-form / streaming window goes straight
+// to its place in the final buffer, which may be peer memory.
+struct PqmfCrop {
+  int64_t lo, len, batch_stride;
+};
 cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int bands, int taps,
-                                  int64_t Ts, void* y, int out_f16, cudaStream_t stream);
+                                  int64_t Ts, void* y, int out_f16, const PqmfCrop* crop, cudaStream_t stream);
 cudaError_t f32_to_f16_launch(const float* x, void* y, int64_t n, cudaStream_t stream);
 // Factorised 4-band / 63-tap synthesis (24 instead of 63 MACs per sample): table built by pqmf_factor_4x63 at
 // plan creation; false = G is not the reference's cosine-modulated bank, keep the direct kernel.
@@ -103,7 +108,7 @@ constexpr int PQMF_FACT_TABLE = 96;
 bool pqmf_factor_4x63(const float* G_host, float* tbl_host);
 bool pqmf_fact_usable(const float* x, int64_t Ts);
 cudaError_t pqmf_synthesis_fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, void* y, int out_f16,
-                                       cudaStream_t stream);
+                                       const PqmfCrop* crop, cudaStream_t stream);
 cudaError_t pqmf_analysis_launch(const float* x, const float* H, int batch, int bands, int taps,
                                  int64_t T, float* y, cudaStream_t stream);
 

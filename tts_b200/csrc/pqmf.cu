@@ -38,10 +38,18 @@ __device__ __forceinline__ float ld_after_wait(const float* p) {
   return v;
 }
 
+// Where the samples go: row b starts at y + b * batch_stride and holds samples [lo, hi) of the synthesis output.
+struct PqmfOut {
+  int64_t batch_stride, lo, hi;
+};
+
 // 16 consecutive output samples of one thread -> global memory as full 32-byte sectors: two 32-byte stores of fp32,
 // or (fp16 waveform: TTSB200_OUT_F16, half the device->host bytes of the result) one 32-byte store of packed halves.
-__device__ __forceinline__ void store16(float* yt, const float (&acc)[4][4], int64_t t_first, int64_t Tout) {
-  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
+// `y0` points at sample 0 of this batch item's row; only samples t in [lo, hi) are stored (the whole row, or the
+// kept range of a long-form / streaming window whose halo samples are computed but never written).
+__device__ __forceinline__ void store16(float* y0, const float (&acc)[4][4], int64_t t_first, int64_t lo, int64_t hi) {
+  float* yt = y0 + t_first;
+  if (t_first >= lo && t_first + 16 <= hi && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
 #pragma unroll
     for (int h = 0; h < 2; ++h)
       asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(yt + 8 * h), "f"(acc[2 * h][0]),
@@ -53,11 +61,12 @@ __device__ __forceinline__ void store16(float* yt, const float (&acc)[4][4], int
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int r = 0; r < 4; ++r)
-        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = acc[i][r];
+        if (t_first + 4 * i + r >= lo && t_first + 4 * i + r < hi) yt[4 * i + r] = acc[i][r];
   }
 }
-__device__ __forceinline__ void store16(__half* yt, const float (&acc)[4][4], int64_t t_first, int64_t Tout) {
-  if (t_first + 16 <= Tout && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
+__device__ __forceinline__ void store16(__half* y0, const float (&acc)[4][4], int64_t t_first, int64_t lo, int64_t hi) {
+  __half* yt = y0 + t_first;
+  if (t_first >= lo && t_first + 16 <= hi && (reinterpret_cast<uintptr_t>(yt) & 31) == 0) {
     uint32_t w[8];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -73,7 +82,7 @@ __device__ __forceinline__ void store16(__half* yt, const float (&acc)[4][4], in
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int r = 0; r < 4; ++r)
-        if (t_first + 4 * i + r < Tout) yt[4 * i + r] = __float2half_rn(acc[i][r]);
+        if (t_first + 4 * i + r >= lo && t_first + 4 * i + r < hi) yt[4 * i + r] = __float2half_rn(acc[i][r]);
   }
 }
 __device__ __forceinline__ void store1(float* y, float v) { *y = v; }
@@ -90,7 +99,7 @@ constexpr int SQ_SMEM_Q = SQ_TILE + 16;          // 8 left + 8 right
 template <typename OutT>
 __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float* x,
                                                                       const float* __restrict__ G,
-                                                                      OutT* __restrict__ y, int Ts) {
+                                                                      OutT* __restrict__ y, int Ts, PqmfOut o) {
   __shared__ __align__(16) float sx[4][SQ_SMEM_Q];
   __shared__ __align__(16) float4 sc[4][16];              // sc[k][off+7] = 4*G[k][4*off+31-r], r=0..3
 
@@ -157,10 +166,9 @@ __global__ void __launch_bounds__(SQ_THREADS) pqmf_synth_4x63_kernel(const float
   }
 
   // each thread owns 4*QPT consecutive outputs, written as 32-byte stores (full sectors, no staging pass)
-  const int64_t Tout = 4 * (int64_t)Ts;
   const int64_t t_first = (int64_t)(q0 + SQ_QPT * tid) * 4;
   static_assert(SQ_QPT == 4, "store16 writes 16 samples per thread");
-  store16(y + (int64_t)b * Tout + t_first, acc, t_first, Tout);
+  store16(y + (int64_t)b * o.batch_stride - o.lo, acc, t_first, o.lo, o.hi);
 }
 
 // ---- factorised N=4, K=63 synthesis ------------------------------------------------------------------------
@@ -178,7 +186,7 @@ constexpr int SF_WIN = SF_TILE + 16;             // v window: q0-8 .. q0+TILE+7
 template <typename OutT>
 __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const float* x,
                                                                            const float* __restrict__ tbl,
-                                                                           OutT* __restrict__ y, int Ts) {
+                                                                           OutT* __restrict__ y, int Ts, PqmfOut o) {
   __shared__ __align__(16) float sv[8][SF_WIN];
   __shared__ __align__(16) float st[PQMF_FACT_TABLE];   // [p][k] modulation, then [p][8] FIR taps
 
@@ -248,20 +256,19 @@ __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const 
       for (int i = 0; i < 4; ++i) acc[i][r] = fmaf(c[e], w[i + base + 2 * e], acc[i][r]);
   }
 
-  const int64_t Tout = 4 * (int64_t)Ts;
   const int64_t t_first = (int64_t)(q0 + 4 * tid) * 4;
-  if (t_first >= Tout) return;
-  store16(y + (int64_t)b * Tout + t_first, acc, t_first, Tout);
+  if (t_first >= o.hi) return;
+  store16(y + (int64_t)b * o.batch_stride - o.lo, acc, t_first, o.lo, o.hi);
 }
 
 // ---- generic (any N, any taps): one thread per output sample ------------------------------------
 template <typename OutT>
 __global__ void pqmf_synth_generic_kernel(const float* __restrict__ x, const float* __restrict__ G,
                                           OutT* __restrict__ y, int N, int K, int pad, int64_t Ts,
-                                          int64_t Tout) {
+                                          int64_t Tout, PqmfOut o) {
   const int b = blockIdx.y;
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= Tout) return;
+  if (t >= Tout || t < o.lo || t >= o.hi) return;
   // j must satisfy (t + j - pad) % N == 0
   int64_t base = t - pad;
   int j0 = (int)(((-base) % N + N) % N);
@@ -271,7 +278,7 @@ __global__ void pqmf_synth_generic_kernel(const float* __restrict__ x, const flo
     if (m < 0 || m >= Ts) continue;
     for (int k = 0; k < N; ++k) acc = fmaf(G[k * K + j], x[((int64_t)b * N + k) * Ts + m], acc);
   }
-  store1(y + (int64_t)b * Tout + t, acc * (float)N);
+  store1(y + (int64_t)b * o.batch_stride + (t - o.lo), acc * (float)N);
 }
 
 __global__ void f32_to_f16_kernel(const float* __restrict__ x, __half* __restrict__ y, int64_t n) {
@@ -345,17 +352,17 @@ bool pqmf_factor_4x63(const float* G, float* tbl) {
 
 namespace {
 template <typename OutT>
-cudaError_t fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, OutT* y, cudaStream_t stream) {
+cudaError_t fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, OutT* y, PqmfOut o, cudaStream_t stream) {
   // shared-memory carve-out preference: a hint, set once per process (first device that launches)
   static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_fact_kernel<OutT>,
                                                         cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   if (carve != cudaSuccess) return carve;
   const dim3 grid(ceil_div(Ts, SF_TILE), batch);
-  return launch_pdl(pqmf_synth_4x63_fact_kernel<OutT>, grid, dim3(SF_THREADS), 0, stream, x, tbl, y, (int)Ts);
+  return launch_pdl(pqmf_synth_4x63_fact_kernel<OutT>, grid, dim3(SF_THREADS), 0, stream, x, tbl, y, (int)Ts, o);
 }
 template <typename OutT>
 cudaError_t direct_launch(const float* x, const float* G, int batch, int bands, int taps, int64_t Ts, OutT* y,
-                          cudaStream_t stream) {
+                          PqmfOut o, cudaStream_t stream) {
   const int K = taps + 1, pad = taps / 2;
   const int64_t Tout = (int64_t)bands * Ts + 2 * pad - taps;
   if (bands == 4 && taps == 62 && Ts < (1 << 30)) {
@@ -365,19 +372,27 @@ cudaError_t direct_launch(const float* x, const float* G, int batch, int bands, 
     static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_kernel<OutT>,
                                                           cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (carve != cudaSuccess) return carve;
-    return launch_pdl(pqmf_synth_4x63_kernel<OutT>, grid, dim3(SQ_THREADS), 0, stream, x, G, y, (int)Ts);
+    return launch_pdl(pqmf_synth_4x63_kernel<OutT>, grid, dim3(SQ_THREADS), 0, stream, x, G, y, (int)Ts, o);
   }
   const dim3 grid(ceil_div(Tout, 256), batch);
-  pqmf_synth_generic_kernel<OutT><<<grid, 256, 0, stream>>>(x, G, y, bands, K, pad, Ts, Tout);
+  pqmf_synth_generic_kernel<OutT><<<grid, 256, 0, stream>>>(x, G, y, bands, K, pad, Ts, Tout, o);
   return cudaGetLastError();
 }
 }  // namespace
 
+namespace {
+PqmfOut make_out(const PqmfCrop* crop, int64_t Tout) {
+  if (crop && crop->len > 0) return PqmfOut{crop->batch_stride, crop->lo, crop->lo + crop->len};
+  return PqmfOut{Tout, 0, Tout};
+}
+}  // namespace
+
 cudaError_t pqmf_synthesis_fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, void* y, int out_f16,
-                                       cudaStream_t stream) {
+                                       const PqmfCrop* crop, cudaStream_t stream) {
   if (batch <= 0 || Ts <= 0) return cudaSuccess;
-  return out_f16 ? fact_launch(x, tbl, batch, Ts, static_cast<__half*>(y), stream)
-                 : fact_launch(x, tbl, batch, Ts, static_cast<float*>(y), stream);
+  const PqmfOut o = make_out(crop, 4 * Ts);
+  return out_f16 ? fact_launch(x, tbl, batch, Ts, static_cast<__half*>(y), o, stream)
+                 : fact_launch(x, tbl, batch, Ts, static_cast<float*>(y), o, stream);
 }
 // usable when whole float4s of every band are in or out of range and aligned
 bool pqmf_fact_usable(const float* x, int64_t Ts) {
@@ -385,11 +400,12 @@ bool pqmf_fact_usable(const float* x, int64_t Ts) {
 }
 
 cudaError_t pqmf_synthesis_launch(const float* x, const float* G, int batch, int bands, int taps,
-                                  int64_t Ts, void* y, int out_f16, cudaStream_t stream) {
+                                  int64_t Ts, void* y, int out_f16, const PqmfCrop* crop, cudaStream_t stream) {
   const int64_t Tout = (int64_t)bands * Ts + 2 * (taps / 2) - taps;
   if (batch <= 0 || Ts <= 0 || Tout <= 0) return cudaSuccess;
-  return out_f16 ? direct_launch(x, G, batch, bands, taps, Ts, static_cast<__half*>(y), stream)
-                 : direct_launch(x, G, batch, bands, taps, Ts, static_cast<float*>(y), stream);
+  const PqmfOut o = make_out(crop, Tout);
+  return out_f16 ? direct_launch(x, G, batch, bands, taps, Ts, static_cast<__half*>(y), o, stream)
+                 : direct_launch(x, G, batch, bands, taps, Ts, static_cast<float*>(y), o, stream);
 }
 
 cudaError_t f32_to_f16_launch(const float* x, void* y, int64_t n, cudaStream_t stream) {

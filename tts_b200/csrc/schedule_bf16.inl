@@ -367,7 +367,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       double bytes = 2.0 * (2.0 * B * C * L + (double)(cfg.res_kernel + 2) * nb * C * C);
       if (fuse_head) {
         const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
-        q.head_out = (to_out && a->out_dtype == TTSB200_OUT_F32) ? static_cast<float*>(a->out) : headf;
+        q.head_out = (to_out && a->out_dtype == TTSB200_OUT_F32 && a->out_keep_len == 0) ? static_cast<float*>(a->out) : headf;
         macs += (double)cfg.proj_kernel * C * cfg.out_channels * L * B;
         bytes = 2.0 * B * C * L + 4.0 * B * cfg.out_channels * L;
         head_done = true;
@@ -418,7 +418,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   {
     const int Cl = plan->stages.back().Cout;
     const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
-    float* dst = (to_out && a->out_dtype == TTSB200_OUT_F32) ? static_cast<float*>(a->out) : headf;
+    float* dst = (to_out && a->out_dtype == TTSB200_OUT_F32 && a->out_keep_len == 0) ? static_cast<float*>(a->out) : headf;
     const int ih = 4 + 3 * S;
     if (!head_done) {
       TcConvParams p = base(plan->tc_head, Lin);

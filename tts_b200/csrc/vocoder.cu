@@ -177,18 +177,34 @@ int finish_output(const ttsb200_plan* plan, const ttsb200_forward_args* a, Launc
   const int B = a->batch;
   const int f16 = a->out_dtype == TTSB200_OUT_F16;
   cudaStream_t st = static_cast<cudaStream_t>(a->stream);
+  const bool windowed = a->out_keep_len > 0;
   if (to_out) {
-    if (f16) {
-      const int64_t n = (int64_t)B * cfg.out_channels * Lin;
+    // `sub` is a workspace buffer whenever a conversion or a window is asked for (see the schedules)
+    const int rows = B * cfg.out_channels;
+    const size_t es = f16 ? 2 : 4;
+    if (f16 && !windowed) {
+      const int64_t n = (int64_t)rows * Lin;
       TTSB_CUDA(ln.run("out.f32_to_f16", -1, 0.0, 6.0 * n, [&] { return f32_to_f16_launch(sub, a->out, n, st); }));
+    } else if (windowed) {
+      const void* src = sub;
+      if (f16)   // only the PQMF synthesis kernels store fp16 into a window themselves
+        return fail(TTSB200_ERR_INVALID, "an output window with fp16 output needs a generator that ends in PQMF synthesis");
+      const size_t dpitch = (size_t)(cfg.out_channels == 1 ? a->out_batch_stride : a->out_keep_len) * es;
+      TTSB_CUDA(cudaMemcpy2DAsync(a->out, dpitch, static_cast<const char*>(src) + (size_t)a->out_keep_lo * es,
+                                  (size_t)Lin * es, (size_t)a->out_keep_len * es, rows, cudaMemcpyDeviceToDevice, st));
     }
     return 0;
   }
   const int N = cfg.pqmf_bands;
-  TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B, (f16 ? 6.0 : 8.0) * N * Lin * B, [&] {
+  const PqmfCrop crop{a->out_keep_lo, a->out_keep_len, a->out_batch_stride};
+  const double out_samples = windowed ? (double)a->out_keep_len * B : (double)N * Lin * B;
+  TTSB_CUDA(ln.run("pqmf.synthesis", -1, 2.0 * (cfg.pqmf_taps + 1) * Lin * B,
+                   4.0 * N * Lin * B + (f16 ? 2.0 : 4.0) * out_samples, [&] {
     if (plan->pqmf_fact && !plan->ctx.pqmf_direct && pqmf_fact_usable(sub, Lin))
-      return pqmf_synthesis_fact_launch(sub, plan->blob + plan->pqmf_fact_off, B, Lin, a->out, f16, st);
-    return pqmf_synthesis_launch(sub, plan->blob + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, f16, st);
+      return pqmf_synthesis_fact_launch(sub, plan->blob + plan->pqmf_fact_off, B, Lin, a->out, f16,
+                                        windowed ? &crop : nullptr, st);
+    return pqmf_synthesis_launch(sub, plan->blob + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, f16,
+                                 windowed ? &crop : nullptr, st);
   }));
   return 0;
 }
@@ -278,8 +294,8 @@ int forward_f32(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   {  // LeakyReLU + ReflectionPad1d + Conv1d k7 + Tanh
     const int Cl = plan->head.Cin;
     const bool to_out = cfg.pqmf_bands == 0 || a->skip_pqmf;
-    const bool f16 = a->out_dtype == TTSB200_OUT_F16;
-    float* dst = (to_out && !f16) ? static_cast<float*>(a->out) : spare0;
+    const bool direct = to_out && a->out_dtype == TTSB200_OUT_F32 && a->out_keep_len == 0;
+    float* dst = direct ? static_cast<float*>(a->out) : spare0;
     ConvParams p = base_params(plan->head, dst, Lin, Lin);
     p.src[0] = make_src(cur, W + plan->head.w_off, Cl, Lin, cfg.proj_kernel, 1, -pp, false, true);
     p.tanh_out = 1;
@@ -485,6 +501,14 @@ int32_t ttsb200_generator_forward(const ttsb200_plan* plan, const ttsb200_forwar
     return fail(TTSB200_ERR_INVALID, "batch too large for one launch (batch * max upsample factor > 65535); split the batch");
   if (a->out_dtype != TTSB200_OUT_F32 && a->out_dtype != TTSB200_OUT_F16)
     return fail(TTSB200_ERR_INVALID, "unknown out_dtype");
+  if (a->out_keep_len < 0 || a->out_keep_lo < 0 ||
+      (a->out_keep_len > 0 &&
+       (a->out_keep_lo + a->out_keep_len > ttsb200_output_length(plan, a->frames, a->pad, a->skip_pqmf) ||
+        a->out_batch_stride < a->out_keep_len)))
+    return fail(TTSB200_ERR_INVALID, "output window outside the result, or out_batch_stride < out_keep_len");
+  if (a->out_keep_len > 0 && (plan->cfg.pqmf_bands == 0 || a->skip_pqmf) && plan->cfg.out_channels > 1 &&
+      a->out_batch_stride != (int64_t)plan->cfg.out_channels * a->out_keep_len)
+    return fail(TTSB200_ERR_INVALID, "a windowed multi-channel output must be dense: out_batch_stride = channels * out_keep_len");
   // The caller's current device need not be the plan's (a generator on cuda:1 called while cuda:0 is current,
   // which the reference supports): launches, attribute calls and events all go to plan->device.
   int prev = 0;
@@ -549,7 +573,7 @@ int32_t ttsb200_pqmf_synthesis(const float* x, const float* G, int32_t batch, in
   if (!x || !G || !y) return fail(TTSB200_ERR_INVALID, "NULL argument");
   if (batch <= 0 || bands <= 0 || taps <= 0 || Ts <= 0 || batch > 65535)
     return fail(TTSB200_ERR_INVALID, "batch/bands/taps/Ts out of range");
-  TTSB_CUDA(pqmf_synthesis_launch(x, G, batch, bands, taps, Ts, y, 0, static_cast<cudaStream_t>(stream)));
+  TTSB_CUDA(pqmf_synthesis_launch(x, G, batch, bands, taps, Ts, y, 0, nullptr, static_cast<cudaStream_t>(stream)));
   return 0;
 }
 

@@ -137,9 +137,13 @@ class GeneratorEngine:
 
     # ---- the hot call
     def forward(self, mel, pad, precision=_lib.F32, skip_pqmf=False, tap_layers=None, profile=None, out=None,
-                out_dtype=None):
+                out_dtype=None, keep=None):
         """mel: CUDA fp32 [B, in_channels, T] on this engine's device. Returns [B, C_out, samples] (fp32, or fp16
-        with ``out_dtype=torch.float16`` / an fp16 ``out``)."""
+        with ``out_dtype=torch.float16`` / an fp16 ``out``).
+
+        ``keep=(lo, n)`` stores only samples [lo, lo + n) of every row, into ``out`` [B, C_out, n] whose batch stride
+        may exceed n (a view into a larger buffer, possibly peer memory): the kept range of a long-form or
+        streaming window lands in place, nothing is sliced or concatenated afterwards."""
         if mel.dim() != 3 or mel.shape[1] != self.cfg.in_channels:
             raise RuntimeError(f"expected mel of shape [B, {self.cfg.in_channels}, T], got {tuple(mel.shape)}")
         if mel.device != self.device:
@@ -151,7 +155,17 @@ class GeneratorEngine:
         lib = _lib.load()
         n_out = self.output_length(T, pad, skip_pqmf)
         ch = 1 if (self.cfg.pqmf_bands and not skip_pqmf) else self.cfg.out_channels
-        if out is not None:
+        if keep is not None:
+            lo, n_keep = int(keep[0]), int(keep[1])
+            if lo < 0 or n_keep <= 0 or lo + n_keep > n_out:
+                raise RuntimeError(f"keep=({lo}, {n_keep}) is outside the {n_out}-sample result")
+            if out is None:
+                out = torch.empty((B, ch, n_keep), dtype=out_dtype or torch.float32, device=self.device)
+            if tuple(out.shape) != (B, ch, n_keep) or out.stride(-1) != 1 or (ch > 1 and not out.is_contiguous()):
+                raise RuntimeError(f"windowed out must be [{B}, {ch}, {n_keep}] with unit sample stride")
+            out_dtype = out.dtype
+            keep = (lo, n_keep, out.stride(0) if B > 1 else max(n_keep, out.stride(0)))
+        elif out is not None:
             out_dtype = out.dtype
             if tuple(out.shape) != (B, ch, n_out) or not out.is_contiguous() or out.device != self.device:
                 raise RuntimeError(f"out must be a contiguous {(B, ch, n_out)} tensor on {self.device}")
@@ -161,9 +175,10 @@ class GeneratorEngine:
         # The module may live on a device that is not the caller's current one (the reference supports that):
         # allocate and look the stream up under the plan's device; the C entry point switches devices itself.
         with torch.cuda.device(self.device):
-            return self._forward(lib, mel, B, T, pad, precision, skip_pqmf, tap_layers, profile, out, out_dtype, ch, n_out)
+            return self._forward(lib, mel, B, T, pad, precision, skip_pqmf, tap_layers, profile, out, out_dtype, ch,
+                                 n_out, keep)
 
-    def _forward(self, lib, mel, B, T, pad, precision, skip_pqmf, tap_layers, profile, out, out_dtype, ch, n_out):
+    def _forward(self, lib, mel, B, T, pad, precision, skip_pqmf, tap_layers, profile, out, out_dtype, ch, n_out, keep):
         if out is None:
             out = torch.empty((B, ch, n_out), dtype=out_dtype, device=self.device)
         stream = torch.cuda.current_stream(self.device)
@@ -177,6 +192,8 @@ class GeneratorEngine:
         a.stream = stream.cuda_stream
         a.skip_pqmf = int(skip_pqmf)
         a.out_dtype = _lib.OUT_F16 if out_dtype == torch.float16 else _lib.OUT_F32
+        if keep is not None:
+            a.out_keep_lo, a.out_keep_len, a.out_batch_stride = keep
         taps = {}
         if tap_layers:
             ids = (ctypes.c_int32 * len(tap_layers))(*tap_layers)

@@ -9,8 +9,11 @@ melgan_generator.py:85-88, the reflect pads inside the network) therefore act at
 they do at a chunk's interior ends lands in the discarded halo.
 
 Exchange: the mel is tiny (80 x 4 B per frame; 16.5 MB for 10 minutes), so every rank holds it and the "halo
-exchange" is a local slice — zero bytes on the wire.  The only collective is the final gather of the waveform
-slices (``all_gather`` over NCCL; 6.6 MB per rank for 10 minutes on 8 GPUs).
+exchange" is a local slice — zero bytes on the wire.  The waveform is not gathered either: ``LongformPlan``
+registers ONE destination buffer on the consuming rank (symmetric memory / CUDA IPC, mapped over NVLink), and every
+rank's last kernel (PQMF synthesis) stores the samples of its own frames — and only those; the halo samples are
+computed but never written — straight into their place in that buffer.  One device-side barrier orders the stores
+before the consumer reads.  No ``all_gather``, no padding buffer, no ``torch.cat``.
 
 Nothing here touches the arithmetic: every sample comes out of the same CUDA path as ``inference()``.
 """
@@ -93,6 +96,10 @@ def longform_inference(generator, mel, group=None, halo=None, infer_fn=None, gat
 
     Returns the full waveform [B, 1, (T + 2*inference_padding) * hop] on every rank (``gather=True``) or only
     this rank's slice plus its (start_sample, end_sample) range (``gather=False``).
+
+    This is the portable form (any backend, any ``infer_fn``; the gloo tests run it on the CPU oracle): slices are
+    exchanged with one ``all_gather``.  On NVLink-connected GPUs use ``LongformPlan``, which places every rank's
+    samples directly in the consumer's buffer instead.
     """
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -120,3 +127,128 @@ def longform_inference(generator, mel, group=None, halo=None, infer_fn=None, gat
     dist.all_gather_into_tensor(recv, send, group=group)
     recv = recv.view(world, B, 1, longest)
     return torch.cat([recv[r, ..., :(pe - ps) * hop] for r, (ps, pe) in enumerate(parts) if pe > ps], dim=-1)
+
+
+class LongformPlan:
+    """Direct-placement long-form inference on NVLink-connected GPUs (BASELINE config 4).
+
+        plan = LongformPlan(generator, n_frames=T, batch=B)      # collective: every rank of the group
+        wav = plan.run(mel)                                       # every rank; the waveform on `dst_rank`, None elsewhere
+
+    Construction allocates the destination ``[B, 1, (T + 2 p) * hop]`` once, on every rank symmetrically, and maps
+    ``dst_rank``'s copy into every other rank's address space:
+
+      * ``symmetric``: ``torch.distributed._symmetric_memory`` (cuMem handles exchanged at rendezvous; peer stores go
+        over NVLink / NVSwitch), with its signal-pad barrier ordering the stores before the consumer's reads;
+      * ``ipc``: CUDA IPC handle of ``dst_rank``'s buffer broadcast to the group, NCCL one-element all_reduce as barrier;
+      * ``gather``: no peer mapping available (not an NVLink box, or a CPU group) — falls back to
+        ``longform_inference`` and says so in ``describe()``.
+
+    ``run`` slices this rank's halo-extended window out of the replicated mel and calls the generator with
+    ``out=`` a view of the destination at its sample offset and ``keep=`` its own sample range, so the PQMF kernel's
+    stores are the only data movement of the whole gather step.  For a generator without PQMF the kept range is
+    placed by one strided device-to-device copy instead (vocoder.cu finish_output).
+    """
+
+    def __init__(self, generator, n_frames, batch=1, group=None, halo=None, dst_rank=0, dtype=torch.float32,
+                 mode=None):
+        import torch.distributed as dist
+        self.g = generator
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.dst_rank = int(dst_rank)
+        self.p = int(generator.inference_padding)
+        self.halo = receptive_halo_frames(generator) if halo is None else int(halo)
+        self.hop = hop_length(generator)
+        self.frames = int(n_frames) + 2 * self.p
+        self.parts = frame_partition(self.frames, self.world)
+        self.n_out = self.frames * self.hop
+        self.batch = int(batch)
+        self.dtype = dtype
+        self.device = next(generator.parameters()).device
+        self._hdl = self._flag = self._ipc_keep = None
+        self.local = self.dest = None
+        self.mode, self.why = self._map_destination(mode)
+
+    # ------------------------------------------------------------------ destination mapping
+    def _map_destination(self, forced):
+        import torch.distributed as dist
+        shape = (self.batch, 1, self.n_out)
+        if self.world == 1 or self.device.type != "cuda":
+            self.local = torch.empty(shape, dtype=self.dtype, device=self.device)
+            self.dest = self.local
+            return "local", "single rank"
+        errors = []
+        for mode in ([forced] if forced else ["symmetric", "ipc", "gather"]):
+            try:
+                if mode == "symmetric":
+                    import torch.distributed._symmetric_memory as symm
+                    grp = self.group if self.group is not None else dist.group.WORLD
+                    buf = symm.empty(shape, dtype=self.dtype, device=self.device)
+                    hdl = symm.rendezvous(buf, grp)
+                    self._hdl, self.local = hdl, buf
+                    self.dest = buf if self.rank == self.dst_rank else hdl.get_buffer(self.dst_rank, shape, self.dtype)
+                    hdl.barrier(channel=0)
+                    return mode, "torch symmetric memory, peer stores over NVLink"
+                if mode == "ipc":
+                    self.local = torch.empty(shape, dtype=self.dtype, device=self.device)
+                    payload = [self.local.untyped_storage()._share_cuda_() if self.rank == self.dst_rank else None]
+                    dist.broadcast_object_list(payload, src=self.dst_rank, group=self.group)
+                    if self.rank == self.dst_rank:
+                        self.dest = self.local
+                    else:
+                        st = torch.UntypedStorage._new_shared_cuda(*payload[0])
+                        self._ipc_keep = st
+                        self.dest = torch.empty(0, dtype=self.dtype, device=st.device).set_(st, 0, shape)
+                        if self.dest.device != self.device:      # the mapping lives on the owner's device index
+                            raise RuntimeError("peer mapping came back on another device index")
+                    self._flag = torch.zeros(1, dtype=torch.float32, device=self.device)
+                    return mode, "CUDA IPC handle of the consumer's buffer, NCCL flag as barrier"
+                if mode == "gather":
+                    return mode, "no peer mapping: " + "; ".join(errors)
+            except Exception as e:   # try the next mechanism
+                errors.append(f"{mode}: {type(e).__name__}: {e}")
+                # every rank must take the same branch: agree on failure
+            finally:
+                pass
+        raise RuntimeError("LongformPlan: no destination mapping available: " + "; ".join(errors))
+
+    def describe(self):
+        return {"mode": self.mode, "why": self.why, "dst_rank": self.dst_rank, "halo_frames": self.halo,
+                "frames_per_rank": [e - s for s, e in self.parts],
+                "recomputed_halo_frames_per_rank": [min(self.frames, e + self.halo) - max(0, s - self.halo) - (e - s)
+                                                    for s, e in self.parts]}
+
+    def _barrier(self):
+        import torch.distributed as dist
+        if self.mode == "symmetric":
+            self._hdl.barrier(channel=0)          # device-side, on the current stream
+        elif self.mode == "ipc":
+            dist.all_reduce(self._flag, group=self.group)   # stream-ordered after this rank's stores
+
+    # ------------------------------------------------------------------ the hot call
+    def run(self, mel):
+        """mel: the full [B, C, T] mel on this rank's device (replicated).  Returns the waveform on dst_rank."""
+        if mel.shape[0] != self.batch or mel.shape[-1] + 2 * self.p != self.frames:
+            raise RuntimeError(f"LongformPlan was built for [{self.batch}, C, {self.frames - 2 * self.p}] mels")
+        if self.mode == "gather":
+            wav = longform_inference(self.g, mel, group=self.group, halo=self.halo)
+            return wav if self.rank == self.dst_rank else None
+        p = self.p
+        s, e = self.parts[self.rank]
+        if e > s:
+            lo, hi = max(0, s - self.halo), min(self.frames, e + self.halo)
+            # window of the replicate-padded mel without materialising the padded copy: clamp the frame indices
+            if p > 0 and (lo < p or hi > self.frames - p):
+                idx = torch.arange(lo - p, hi - p, device=mel.device).clamp_(0, mel.shape[-1] - 1)
+                window = mel.index_select(-1, idx)
+            else:
+                window = mel[..., lo - p:hi - p].contiguous()
+            out = self.dest[..., s * self.hop:e * self.hop]
+            self.g.inference_padded(window, 0, out=out, keep=((s - lo) * self.hop, (e - s) * self.hop))
+        self._barrier()
+        return self.local if self.rank == self.dst_rank else None
+
+    def close(self):
+        self.dest = self.local = self._hdl = self._ipc_keep = None

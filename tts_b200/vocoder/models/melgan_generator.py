@@ -100,18 +100,19 @@ class MelganGenerator(nn.Module):
 
     _SKIP_PQMF = True   # MultibandMelganGenerator.inference appends PQMF synthesis (multiband_melgan_generator.py:38)
 
-    def _run(self, c, pad, skip_pqmf, tap_layers=None, profile=None, out=None, out_dtype=None):
+    def _run(self, c, pad, skip_pqmf, tap_layers=None, profile=None, out=None, out_dtype=None, keep=None):
         eng = self._get_engine()
         c = c.detach().to(device=eng.device, dtype=torch.float32, non_blocking=True)   # async when c is pinned
         prec = _lib.PRECISIONS[self.precision]
         return eng.forward(c, int(pad), prec, skip_pqmf=skip_pqmf, tap_layers=tap_layers, profile=profile, out=out,
-                           out_dtype=out_dtype)
+                           out_dtype=out_dtype, keep=keep)
 
-    def inference_padded(self, c, pad, out=None):
+    def inference_padded(self, c, pad, out=None, keep=None):
         """``inference`` with an explicit padding for this call only.  Long-form and streaming windows run with
         padding 0 (tts_b200/longform.py, streaming.py); they must not change ``inference_padding`` on a module
-        that request threads share (TTS/server/server.py:64,82)."""
-        return self._run(c, int(pad), self._SKIP_PQMF, out=out)
+        that request threads share (TTS/server/server.py:64,82).  ``keep=(lo, n)`` with ``out`` stores only that
+        sample range, in place (GeneratorEngine.forward)."""
+        return self._run(c, int(pad), self._SKIP_PQMF, out=out, keep=keep)
 
     # ------------------------------------------------------------------ reference surface
     def forward(self, c):
