@@ -7,8 +7,11 @@
 //   XA   (shared, canonical [CP/8][RS][8] bf16, double-buffered across items)  lrelu(x): A operand of the
 //        dilated conv — each tap is the same tile at a different start row, so only the descriptor moves;
 //   XR[t] (TMEM, bf16, CP/2 columns)  raw x of tile t: A operand of the 1x1 shortcut (A-from-TMEM MMA);
-//   D1[t] (TMEM, fp32, CP columns)    dilated-conv accumulator, pre-loaded with the bias row by tcgen05.st so the
-//        epilogue has no bias add; its epilogue writes h = lrelu(D1 + b1) as bf16
+//   D1[t] (TMEM, fp32, CP columns)    dilated-conv accumulator.  Its FIRST MMA is the bias: A = a constant "ones"
+//        operand in TMEM (8 columns, K0 = K1 = 1), B = the bias as a [CP x 16] operand in shared memory (K-row 0 =
+//        bf16 high part, K-row 1 = bf16 remainder, so the sum carries ~16 mantissa bits), accumulate off — no
+//        epilogue adds or pre-loads a bias (tcgen05.st runs at 128 B/cycle/SM, tests/cuda/epi_probe.cu: writing two
+//        bias rows per tile and block cost as many cycles as the MMAs).  Its epilogue writes h = lrelu(D1) as bf16
 //        over the low CP/2 columns of the same region -> A operand of the 1x1 conv, never touching smem;
 //   D2[t] (TMEM, fp32, CP columns)    W2 h + S x accumulator = x of the next block.
 //   W1 / W2S (shared)  weights of the current block, or of all blocks when they fit (then loaded once per CTA).
@@ -73,7 +76,7 @@ struct Bars {
 // TAIL: what follows the last block — 0 the stack output is stored, 1 fused output head, 2 fused transposed conv
 // of the next stage.  A template parameter so each variant carries (and allocates registers for) its own code only.
 template <int CP, int KT, int CS, int TAIL>
-__global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP / 2 <= 256) ? 2 : 1)
+__global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP / 2 + 8 <= 256) ? 2 : 1)
     tc_stack_kernel(const __grid_constant__ TcStackParams p) {
   constexpr int NT = SERVICE_THREADS + KT * CS * 128;
   constexpr int GROUP_THREADS = CS * 128;
@@ -82,8 +85,9 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   constexpr int TR = KT * 128;        // staged rows owned by the chain
   constexpr int CW = CP / CS;         // channels per epilogue thread
   constexpr int TCOLS = 5 * CP / 2;   // TMEM columns per tile: D1 | D2 | XR
-  static_assert(KT * TCOLS <= 512, "TMEM budget");
-  constexpr uint32_t TMEM_ALLOC = KT * TCOLS <= 128 ? 128 : KT * TCOLS <= 256 ? 256 : 512;   // <= 256: two CTAs share an SM
+  constexpr int ONES_COL = KT * TCOLS;   // 8 columns behind the tiles: the constant A operand of the bias MMAs
+  static_assert(KT * TCOLS + 8 <= 512, "TMEM budget");
+  constexpr uint32_t TMEM_ALLOC = KT * TCOLS + 8 <= 128 ? 128 : KT * TCOLS + 8 <= 256 ? 256 : 512;   // <= 256: two CTAs share an SM
   static_assert(CW % 8 == 0, "CP must be a multiple of 16");
   // Ring mode (wide stages, one tile per CTA): a block's weights do not fit in shared memory, so they stream
   // through a ring of [RING_KB channels x CP columns] chunks in exactly the order the MMAs consume them.
@@ -102,12 +106,14 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   constexpr uint32_t SLOT_BYTES = RING_KB * CP * 2;
   constexpr int NCH = (TAPS + 2) * NK;                   // chunks per block
 
+  // Biases: every accumulator's first MMA is a bias MMA (see the header) — except in ring mode, whose shared memory
+  // is full (two x tiles + four weight slots) and whose single tile per CTA is MMA-bound anyway: there the epilogues
+  // pre-load the accumulators with the bias rows by tcgen05.st as before.
+  constexpr bool BIAS_MMA = !RING;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) Bars bars;
   __shared__ uint32_t tmem_base_s;
-  __shared__ __align__(16) float s_bias[TC_STACK_MAX_BLOCKS][2][CP];
-  __shared__ __align__(16) float s_bias_head[16];
-  __shared__ __align__(16) float s_bias_up[256];
+  __shared__ __align__(16) float s_bias[RING ? TC_STACK_MAX_BLOCKS : 1][2][RING ? CP : 4];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = p.guard, RS = TR + 2 * G;
@@ -130,6 +136,17 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   uint8_t* sW = smem + 2 * xa_bytes;   // [set][W1 | W2S]
   uint8_t* sWH = sW + (RING ? (size_t)wsets * SLOT_BYTES : (size_t)wsets * (W1_BYTES + W2_BYTES));   // head weights
   const uint32_t wh_bytes = head ? (uint32_t)p.head_taps * CP * 16 * 2 : 0;
+  // Bias operands (B of the bias MMAs): per block {b1, b2 + bs} as [CP rows x 16 B] planes (K-rows 0/1 = hi/lo), the
+  // fused tail's bias, and one all-zero plane every descriptor points its second K-plane at (LBO = zero - start).
+  const int tail_n = head ? 16 : up ? p.up_n : 0;
+  uint8_t* sB = sWH + (head ? wh_bytes : (up && p.up_mode == 1) ? up_bytes : 0);
+  uint8_t* sBtail = sB + (size_t)nb * 2 * CP * 16;
+  uint8_t* sBzero = sBtail + (size_t)tail_n * 16;
+  const uint32_t bzero = smem_u32(sBzero);
+  auto bias_desc = [&](const uint8_t* bp) {
+    const uint32_t a = smem_u32(bp);
+    return make_desc(a, bzero - a, 128);
+  };
 
   const int n_items = p.n_chains * p.batch;
 
@@ -161,13 +178,27 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   constexpr int PRODUCER_WARP = KT * CS * 4, MMA_WARP = PRODUCER_WARP + 1;
   constexpr int THIRD_WARP = MMA_WARP + 1;       // ring mode: issues the odd weight chunks; else: pointwise MMA issuer
   if (warp == PRODUCER_WARP) tmem_alloc(&tmem_base_s, TMEM_ALLOC);
-  for (int e = tid; e < nb * 2 * CP; e += NT) {
-    const int blk = e / (2 * CP), r = e - blk * 2 * CP;
-    s_bias[blk][r / CP][r % CP] = r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP];
+  if (!BIAS_MMA) {
+    for (int e = tid; e < nb * 2 * CP; e += NT) {
+      const int blk = e / (2 * CP), r = e - blk * 2 * CP;
+      s_bias[RING ? blk : 0][r / CP][RING ? r % CP : 0] = r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP];
+    }
+  } else {
+    auto put_bias = [](uint8_t* dst, float b) {
+      const __nv_bfloat16 hi = __float2bfloat16(b);
+      const __nv_bfloat16 lo = __float2bfloat16(b - __bfloat162float(hi));
+      *reinterpret_cast<uint4*>(dst) =
+          make_uint4((uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16), 0u, 0u, 0u);
+    };
+    for (int e = tid; e < nb * 2 * CP; e += NT) {
+      const int blk = e / (2 * CP), r = e - blk * 2 * CP;
+      put_bias(sB + (size_t)e * 16, r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP]);
+    }
+    for (int e = tid; e < tail_n; e += NT) put_bias(sBtail + (size_t)e * 16, head ? p.head_b[e] : p.up_b[e]);
+    const int zn = CP > tail_n ? CP : tail_n;
+    for (int e = tid; e < zn; e += NT) *reinterpret_cast<uint4*>(sBzero + (size_t)e * 16) = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async();   // the MMAs read these through the async proxy
   }
-  if (head && tid < 16) s_bias_head[tid] = p.head_b[tid];
-  if (up)
-    for (int e = tid; e < p.up_n; e += NT) s_bias_up[e] = p.up_b[e];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -353,6 +384,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         const int set = wsets == 1 ? 0 : blk;
         const uint32_t w1 = smem_u32(sW + (size_t)set * (W1_BYTES + W2_BYTES));
         const int d = p.dil[blk];
+        const uint64_t b1_desc = bias_desc(sB + (size_t)(2 * blk) * CP * 16);
         if (wsets == 1) mbar_wait(&bars.w1_full[0], gb & 1);
         else if (it == 0) mbar_wait(&bars.w1_full[set], 0);
         // Issue order: tap j of tile t reads rows shifted by (j - 1) d, so taps 0 and 1 need tiles <= t only and
@@ -380,6 +412,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             issue_taps(t - 1, 2, 3);
             if (leader) umma_commit(&bars.d1_full[t - 1]);
           }
+          if (leader) umma_bf16_ts(tbase + t * TCOLS, tbase + ONES_COL, b1_desc, idesc, 0);   // D1[t] <- b1 (overwrites)
           issue_taps(t, 0, 2);
           __syncwarp();
           tr(110 + t);
@@ -420,6 +453,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         const uint32_t ph = gb & 1;
         const int set = wsets == 1 ? 0 : blk;
         const uint32_t w2 = smem_u32(sW + (size_t)set * (W1_BYTES + W2_BYTES)) + W1_BYTES;
+        const uint64_t b2_desc = bias_desc(sB + (size_t)(2 * blk + 1) * CP * 16);
         if (wsets == 1) mbar_wait(&bars.w2_full[0], n_w2++ & 1);
         else if (it == 0) mbar_wait(&bars.w2_full[set], 0);
         tr(113);
@@ -431,6 +465,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           tc_fence_after();
           const uint32_t tcol = tbase + t * TCOLS;
           if (leader) {
+            umma_bf16_ts(tcol + CP, tbase + ONES_COL, b2_desc, idesc, 0);   // D2[t] <- b2 + bs (overwrites)
 #pragma unroll
             for (int kk = 0; kk < KS; ++kk)
               umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
@@ -470,6 +505,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
           tc_fence_after();
           if (leader) {
+            umma_bf16_ts(tbase + t * TCOLS, tbase + ONES_COL, bias_desc(sBtail), idesc_h, 0);   // head accumulator <- bias
             for (int j = 0; j < p.head_taps; ++j) {
               const uint32_t a_row = xa + (uint32_t)(G + t * 128 + j - hh) * 16;
               const uint32_t w_tap = wh + (uint32_t)j * (CP * 16 * 2);
@@ -502,6 +538,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           tc_fence_after();
           tr(140 + t);
           if (leader) {
+            umma_bf16_ts(tbase + t * TCOLS, tbase + ONES_COL, bias_desc(sBtail), idesc_u, 0);   // accumulator <- bias
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
               const uint32_t a_row = xa + (uint32_t)(G + t * 128 - j) * 16;
@@ -539,6 +576,12 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     Tracer tr = make_tracer(p.trace, 1 + t, m == 0 && cs == 0 && !DBG(512));
     Tracer trw = make_tracer(p.trace, 1 + KT + warp, lane == 0 && !DBG(512));   // per-warp arrival times
     uint32_t n_d1 = 0;                          // completed d1_full rounds (blocks, plus the fused head)
+    if (BIAS_MMA && t == 0 && cs == 0) {
+      // constant A operand of every bias MMA: K0 = K1 = 1.0 (bf16 pair in column 0), K2..15 = 0; published with the
+      // first item's prologue (tcgen05.wait::st + fence + arrive), which every issuer passes before its first MMA
+      const uint32_t ones[8] = {0x3F803F80u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+      tmem_st8(tbase + ((uint32_t)(q4 * 32) << 16) + ONES_COL, ones);
+    }
 
     // First half of an item's prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place in XA.  It touches
     // neither D1 nor D2, so in kernels with a fused tail it runs for item it+1 while item it's tail MMAs execute
@@ -632,7 +675,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         if (tau == 0) row_store(-1 - g0, z);
         if (tau == L - 1) row_store(L - g0, z);
       };
-      // Accumulators start from the bias: D[t] <- bias row, then every MMA accumulates (no FADD in the epilogues).
+
+      // Ring mode only: accumulators start from the bias row (tcgen05.st), then every MMA accumulates.
       auto init_acc = [&](uint32_t taddr, const float* bias_row) {
         uint32_t bv[CW];
         const float4* src = reinterpret_cast<const float4*>(bias_row + c0);
@@ -643,6 +687,17 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           bv[4 * i + 2] = __float_as_uint(f.z); bv[4 * i + 3] = __float_as_uint(f.w);
         }
         tmem_st<CW>(taddr + c0, bv);
+      };
+      auto init_acc16 = [&](uint32_t taddr, const float* bias_row, int c) {
+        uint32_t bv[16];
+        const float4* src = reinterpret_cast<const float4*>(bias_row + c0 + c);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 f = src[i];
+          bv[4 * i] = __float_as_uint(f.x); bv[4 * i + 1] = __float_as_uint(f.y);
+          bv[4 * i + 2] = __float_as_uint(f.z); bv[4 * i + 3] = __float_as_uint(f.w);
+        }
+        tmem_st<16>(taddr + c0 + c, bv);
       };
 
       // Where this thread's row goes in XA for the whole item (byte offsets within a plane, -1 = nowhere): its own
@@ -693,35 +748,16 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           }
         }
       };
-      // 16 accumulator columns <- their bias values
-      auto init_acc16 = [&](uint32_t taddr, const float* bias_row, int c) {
-        uint32_t bv[16];
-        const float4* src = reinterpret_cast<const float4*>(bias_row + c0 + c);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float4 f = src[i];
-          bv[4 * i] = __float_as_uint(f.x); bv[4 * i + 1] = __float_as_uint(f.y);
-          bv[4 * i + 2] = __float_as_uint(f.z); bv[4 * i + 3] = __float_as_uint(f.w);
-        }
-        tmem_st<16>(taddr + c0 + c, bv);
-      };
 
       // ---- prologue: raw x tile -> XR[t] (TMEM, bf16) and lrelu(x) in place; accumulators <- block 0 biases
       if (EARLY_STAGE) {
         if (!staged) stage_item(it);
         tr(200);
-        init_acc(tlane, s_bias[0][0]);
-        if (!SPLIT_E2) init_acc(tlane + CP, s_bias[0][1]);
-        tmem_wait_st();
+        tmem_wait_st();          // raw x in XR[t] (and, first item, the ones operand)
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(&bars.xa_ready[t]);
-        if (SPLIT_E2) {
-          init_acc(tlane + CP, s_bias[0][1]);
-          tmem_wait_st();
-          tc_fence_before();
-          mbar_arrive(&bars.xr_ready[t]);
-        }
+        if (SPLIT_E2) mbar_arrive(&bars.xr_ready[t]);
         tr(201);
       } else {
       mbar_wait_relaxed(&bars.x_full[buf], (it >> 1) & 1);
@@ -734,12 +770,9 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           const uint4 u = *reinterpret_cast<const uint4*>(src + (size_t)pl * plane_bytes);
           w[4 * pl] = u.x; w[4 * pl + 1] = u.y; w[4 * pl + 2] = u.z; w[4 * pl + 3] = u.w;
         }
-        // critical half first (what the dilated conv needs), then raw x and the D2 bias row for the 1x1 pair
-        init_acc(tlane, s_bias[0][0]);
-        if (!SPLIT_E2) {
-          tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
-          init_acc(tlane + CP, s_bias[0][1]);
-        }
+        // critical half first (what the dilated conv needs), then raw x for the 1x1 shortcut
+        if (!BIAS_MMA) init_acc(tlane, s_bias[0][0]);
+        if (!SPLIT_E2) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
         uint32_t a[CW / 2];
 #pragma unroll
         for (int i = 0; i < CW / 2; ++i) a[i] = lrelu_bf16x2(w[i], slope2);
@@ -750,7 +783,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         mbar_arrive(&bars.xa_ready[t]);
         if (SPLIT_E2) {
           tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
-          init_acc(tlane + CP, s_bias[0][1]);
+          if (!BIAS_MMA) init_acc(tlane + CP, s_bias[0][1]);
           tmem_wait_st();
           tc_fence_before();
           mbar_arrive(&bars.xr_ready[t]);
@@ -819,21 +852,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
               xa_store16(c, a8, last && up);
               if (!last) {
                 tmem_st8(tlane + 2 * CP + (c0 + c) / 2, w8);
-                init_acc16(tlane, s_bias[blk + 1][0], c);
-                if (!SPLIT_E2) init_acc16(tlane + CP, s_bias[blk + 1][1], c);
-              }
-            }
-            if (last && head) {
-              uint32_t bv[16];
-#pragma unroll
-              for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_head[i]);
-              tmem_st<16>(tlane, bv);            // head accumulator <- head bias
-            } else if (last) {
-              for (int c = cs * UW; c < (cs + 1) * UW; c += 16) {   // transposed-conv accumulator <- its bias
-                uint32_t bv[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_up[c + i]);
-                tmem_st<16>(tlane + c, bv);
+                if (!BIAS_MMA) init_acc16(tlane, s_bias[RING ? blk + 1 : 0][0], c);
               }
             }
             tr(225);
@@ -844,12 +863,13 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             mbar_arrive(&bars.xa_ready[t]);
             tr(221);
             trw(321);
-            // Off the critical path: the D2 bias row, needed only by the 1x1 pair after the next dilated conv.
             if (SPLIT_E2 && !last) {
-              init_acc(tlane + CP, s_bias[blk + 1][1]);
-              tmem_wait_st();
-              tc_fence_before();
-              mbar_arrive(&bars.xr_ready[t]);
+              if (!BIAS_MMA) {   // off the critical path: the D2 bias row, needed only after the next dilated conv
+                init_acc(tlane + CP, s_bias[RING ? blk + 1 : 0][1]);
+                tmem_wait_st();
+                tc_fence_before();
+              }
+              mbar_arrive(&bars.xr_ready[t]);   // raw x went out with the chunks above
             }
           } else if (!last || tail) {
             // Narrow stages (two CTAs per SM, instruction-issue bound): everything at once — one TMEM load and one
@@ -858,22 +878,6 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             tmem_ld_nw<CW>(tlane + CP + c0, v);
             tmem_wait_ld();
             tr(223);
-            if (!last) {
-              if (!DBG(16)) init_acc(tlane, s_bias[blk + 1][0]);
-              if (!SPLIT_E2 && !DBG(16)) init_acc(tlane + CP, s_bias[blk + 1][1]);
-            } else if (head) {
-              uint32_t bv[16];
-#pragma unroll
-              for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_head[i]);
-              tmem_st<16>(tlane, bv);            // head accumulator <- head bias
-            } else {
-              for (int c = cs * UW; c < (cs + 1) * UW; c += 16) {   // transposed-conv accumulator <- its bias
-                uint32_t bv[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) bv[i] = __float_as_uint(s_bias_up[c + i]);
-                tmem_st<16>(tlane + c, bv);
-              }
-            }
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
             if (!SPLIT_E2 && !last && !DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
@@ -893,7 +897,6 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             trw(321);
             if (SPLIT_E2 && !last) {
               if (!DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
-              if (!DBG(16)) init_acc(tlane + CP, s_bias[blk + 1][1]);
               tmem_wait_st();
               tc_fence_before();
               mbar_arrive(&bars.xr_ready[t]);
@@ -1011,7 +1014,14 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   if (warp == PRODUCER_WARP) tmem_dealloc(tbase, TMEM_ALLOC);
 }
 
-constexpr size_t SMEM_MAX = 227 * 1024 - 8 * 1024;   // static: barriers + bias tables (<= 4*2*192*4 B)
+constexpr size_t SMEM_MAX = 227 * 1024 - 8 * 1024;   // static: barriers, TMEM base, ring mode's fp32 bias rows (6 KB)
+
+// Bias operands of the bias MMAs: {b1, b2 + bs} per block and the fused tail's bias as [n x 16 B] planes, one zero plane.
+size_t bias_smem_bytes(const TcStackParams& p) {
+  if (p.cp > 96) return 0;   // ring mode pre-loads its accumulators instead
+  const size_t tail_n = p.head_w ? 16 : p.up_w ? (size_t)p.up_n : 0;
+  return ((size_t)p.nblocks * 2 * p.cp + tail_n + std::max<size_t>(p.cp, tail_n)) * 16;
+}
 
 // cudaFuncSetAttribute is per device and costs a driver call: done once per (instantiation, device).
 template <int CP, int KT, int CS, int TAIL>
@@ -1029,7 +1039,7 @@ cudaError_t launch(const TcStackParams& p, size_t smem, int grid, int device, cu
 
 }  // namespace
 
-int tc_stack_ctas_per_sm(int cp) { return tc_stack_kt(cp) * 5 * cp / 2 <= 256 ? 2 : 1; }
+int tc_stack_ctas_per_sm(int cp) { return tc_stack_kt(cp) * 5 * cp / 2 + 8 <= 256 ? 2 : 1; }
 
 int tc_stack_cs(int cp) { return cp >= 128 ? 4 : cp == 96 ? 2 : 1; }
 
@@ -1089,14 +1099,14 @@ bool tc_stack_configure(TcStackParams& p) {
   if (p.kt * 128 - 2 * (p.sum_d + hh) < 32 || p.guard + p.sum_d + hh > 127) return false;
   const size_t xa = 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;
   const size_t wset = (size_t)(TAPS + 2) * p.cp * p.cp * 2;
-  const size_t wh = head ? (size_t)p.head_taps * p.cp * 16 * 2 : 0;
+  const size_t wh = (head ? (size_t)p.head_taps * p.cp * 16 * 2 : 0) + bias_smem_bytes(p);
   // two CTAs per SM when the TMEM footprint allows it: each then gets half of the shared memory
   const size_t budget = tc_stack_ctas_per_sm(p.cp) == 2 ? SMEM_MAX / 2 - 1024 : SMEM_MAX;
   if (p.cp > 96) {   // ring mode: w_sets = number of [RING_KB x cp] chunk slots
     if (head) return false;
     const size_t slot = (size_t)RING_KB * p.cp * 2;
-    if (xa + 4 * slot > budget) return false;
-    const size_t n = (budget - xa) / slot;
+    if (xa + wh + 4 * slot > budget) return false;
+    const size_t n = (budget - xa - wh) / slot;
     p.w_sets = (int)(n > RING_MAX_SLOTS ? RING_MAX_SLOTS : n);
     return true;
   }
@@ -1117,8 +1127,11 @@ bool tc_stack_configure(TcStackParams& p) {
 cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, int device, cudaStream_t stream);
 
 size_t tc_stack_smem_bytes(const TcStackParams& p) {
-  if (p.cp > 96) return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * RING_KB * p.cp * 2;
-  return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
+  if (p.cp > 96)
+    return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * RING_KB * p.cp * 2 +
+           bias_smem_bytes(p);
+  return bias_smem_bytes(p) + 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 +
+         (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
          (p.head_w ? (size_t)p.head_taps * p.cp * 16 * 2 : 0) +
          (p.up_w && p.up_mode == 1 ? (size_t)2 * p.cp * p.up_n * 2 : 0);
 }

@@ -119,21 +119,29 @@ class GeneratorEngine:
     MAX_WORKSPACES = 8
 
     def _workspace(self, nbytes, stream_key):
-        """Scratch for one forward, keyed by the launch stream and nothing else: work on one stream is serialised
-        by the stream, so the Flask request threads that share a module (TTS/server/server.py:64,82) and all launch
-        on the default stream share ONE workspace instead of leaking one per thread.  At most MAX_WORKSPACES are
-        kept (least recently used first out); an evicted tensor goes back to torch's caching allocator, which only
-        reuses the block in stream order of the stream it was allocated on — the stream that may still be running
-        kernels on it — so eviction is safe while work is in flight."""
+        """(scratch tensor, launch lock) for one forward, keyed by the launch stream and nothing else.
+
+        The Flask request threads that share a module (TTS/server/server.py:64,82) all launch on the default stream;
+        they share ONE workspace instead of leaking one per thread.  That is safe only if the ~10 launches of one
+        forward are not interleaved with another thread's on the same stream (the stream orders kernels, not launch
+        sequences), so the caller holds the entry's lock while it enqueues; the enqueue takes tens of microseconds.
+        At most MAX_WORKSPACES entries are kept (least recently used first out); an evicted tensor goes back to
+        torch's caching allocator, which reuses the block only in stream order of the stream it was allocated on —
+        the stream that may still be running kernels on it — so eviction is safe while work is in flight."""
         with self._lock:
-            ws = self._ws.get(stream_key)
-            if ws is None or ws.numel() < nbytes:
-                ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
-                self._ws[stream_key] = ws
+            ent = self._ws.get(stream_key)
+            if ent is None:
+                ent = self._ws[stream_key] = [None, threading.Lock()]
             self._ws.move_to_end(stream_key)
             while len(self._ws) > self.MAX_WORKSPACES:
                 self._ws.popitem(last=False)
-        return ws
+        return ent
+
+    @staticmethod
+    def _grow(ent, nbytes, device):
+        if ent[0] is None or ent[0].numel() < nbytes:     # under ent's lock
+            ent[0] = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        return ent[0]
 
     # ---- the hot call
     def forward(self, mel, pad, precision=_lib.F32, skip_pqmf=False, tap_layers=None, profile=None, out=None,
@@ -183,12 +191,11 @@ class GeneratorEngine:
             out = torch.empty((B, ch, n_out), dtype=out_dtype, device=self.device)
         stream = torch.cuda.current_stream(self.device)
         ws_bytes = self.workspace_bytes(B, T, pad, precision)
-        ws = self._workspace(ws_bytes, stream.cuda_stream)
+        ent = self._workspace(ws_bytes, stream.cuda_stream)
         a = _lib.ForwardArgs()
         a.mel = mel.data_ptr()
         a.batch, a.frames, a.pad, a.precision = B, T, pad, precision
         a.out = out.data_ptr()
-        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         a.stream = stream.cuda_stream
         a.skip_pqmf = int(skip_pqmf)
         a.out_dtype = _lib.OUT_F16 if out_dtype == torch.float16 else _lib.OUT_F32
@@ -208,7 +215,10 @@ class GeneratorEngine:
             a.tap_out = ptrs
         if profile is not None:
             a.profile = profile._h
-        _lib.check(lib.ttsb200_generator_forward(self._h, ctypes.byref(a)))
+        with ent[1]:          # one launch sequence at a time per stream (see _workspace)
+            ws = self._grow(ent, ws_bytes, self.device)
+            a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+            _lib.check(lib.ttsb200_generator_forward(self._h, ctypes.byref(a)))
         return (out, taps) if tap_layers else out
 
     def forward_host(self, mel_host, pad, precision=_lib.F32):
