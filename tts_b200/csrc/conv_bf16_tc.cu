@@ -105,6 +105,16 @@ __device__ __forceinline__ void conv_epilogue(const TcConvParams& p, const TcGro
     if (!(p.debug & 2))
 #endif
     if (REINIT) bias_to_acc(trow, c, nc, ncols, s_bias);
+#ifdef TTSB_STACK_TRACE
+    if (p.debug & 8) {   // knock-out: no global stores
+      for (int u = 0; u < 8; ++u)
+        if (++r == f) {
+          r = 0;
+          ++plane;
+        }
+      continue;
+    }
+#endif
     if (to_canon) {
       uint32_t w[16];
       if (act) {
@@ -176,6 +186,66 @@ __device__ __forceinline__ void conv_epilogue(const TcConvParams& p, const TcGro
         ++plane;
       }
     __syncwarp();   // edge lanes took other branches: reconverge before the next warp-wide tcgen05.ld
+  }
+}
+
+// Interior tiles of the activation-resident kernel: every GEMM row of the tile is valid and all its output rows lie
+// clear of the sequence ends (no mirror / zero margins to write), so the epilogue is load -> convert -> store with the
+// addresses advanced incrementally: ~45 instructions per 32-column batch instead of the general routine's ~120 with
+// its per-row edge predicates.  The accumulator already holds the bias (bias MMA) and is not re-initialised.
+template <bool ACT>
+__device__ __forceinline__ void conv_epilogue_fast(const TcConvParams& p, const TcGroup& G, uint32_t trow, int q4, int hf,
+                                                   int lane, int t0, int b, float slope) {
+  const int ncols = G.ncols, f = p.up_f;
+  const int q = t0 + q4 * 32 + lane;
+  const int u0 = (G.col_first >> 3) + hf * 4;          // first 8-column unit of this warp's first batch
+  int plane = u0 / f, r = u0 - plane * f;
+  const int64_t prow = (int64_t)p.out_plane_rows * 8;  // elements per plane
+  __nv_bfloat16* ptr = p.out_c + (int64_t)b * p.out_batch_stride + (int64_t)plane * prow +
+                       (int64_t)(p.out_halo + q * f - p.up_P + r) * 8;
+  const bool paired = (f & 1) == 0 && ((p.out_halo - p.up_P) & 1) == 0;
+  const int64_t wrap = prow - (int64_t)f * 8;          // pointer step when the phase wraps into the next plane
+  auto step = [&](int units) {                         // advance (phase, pointer) by `units` 8-column units
+    r += units;
+    ptr += units * 8;
+    if (r >= f) {                                      // units <= 2 and f >= units, or f == 1 handled by the loop below
+      r -= f;
+      ptr += wrap;
+    }
+  };
+  for (int c = hf * 32; c < ncols; c += 64) {
+    const int nc = min(32, ncols - c);
+    uint32_t v[32], w[16];
+    tmem_ld16_nw(trow + c, v);
+    if (nc > 16) tmem_ld16_nw(trow + c + 16, v + 16);
+    tmem_wait_ld();
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      float lo = __uint_as_float(v[2 * i]), hi = __uint_as_float(v[2 * i + 1]);
+      if (ACT) {
+        lo = lrelu_f(lo, slope);
+        hi = lrelu_f(hi, slope);
+      }
+      w[i] = pack_bf16x2(lo, hi);
+    }
+    const int nu = nc >> 3;                            // 2 or 4 units in this batch
+    if (paired) {
+#pragma unroll
+      for (int u = 0; u < 4; u += 2) {
+        if (u < nu) st_global_v8(ptr, w + 4 * u);
+        step(2);
+      }
+      step(2);                                         // the partner warp's batch: 4 units
+      step(2);
+    } else {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u < nu) *reinterpret_cast<uint4*>(ptr) = make_uint4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
+        step(1);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) step(1);
+    }
   }
 }
 
@@ -500,6 +570,219 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
   if (warp == 0) tmem_dealloc(tbase, 2 * acc_stride);
 }
 
+// ---- persistent, activation-resident variant (weights streamed) -------------------------------------------
+// The weights-resident kernel above must keep its column groups narrow (64-128 columns: a whole group's weights have
+// to fit in shared memory), and an SS MMA with M = 128 fetches 4 KB of A per K-step however narrow N is, so at
+// N = 64 the tensor pipe idles behind the shared-memory reads (measured 50 cycles per MMA against a 32-cycle floor;
+// convT@3 ran at 22 % of the BF16 peak).  Here the roles are swapped: a CTA keeps one (utterance, time tile) unit's
+// ACTIVATION tile resident, walks ALL column groups of the layer over it with N up to 256 per MMA (A and B reads
+// balance, the pipe runs at its N/2-cycle floor), and the weights stream from L2 through a ring of >= 16 KB stages
+// fed by two producer warps.  Two TMEM accumulators alternate between groups, so the epilogue of group g overlaps
+// the MMAs of group g + 1.  The bias is the first MMA of every group (accumulate off): A = a constant [128 x 16]
+// operand in shared memory with K0 = K1 = 1, B = the group's bias as hi / lo bf16 K-rows, second K-plane of both
+// pointed at one zero plane — so the epilogue neither adds a bias nor re-loads accumulators through tcgen05.st
+// (128 B/cycle/SM).  Weight traffic is units x layer weights from L2 (44-132 MB per launch at cfg2).
+constexpr int CS_MAX_STAGES = 8;
+constexpr int CS_MAX_COLS = 2048;          // all columns of a layer (bias table)
+constexpr int NTS = NT + 32;               // + second weight producer
+
+__global__ void __launch_bounds__(NTS) tc_convs_kernel(const __grid_constant__ TcConvParams p, const int kb_stage,
+                                                       const int nst, const int na, const int n_tiles, const int batch) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t a_full[2], a_free[2], w_full[CS_MAX_STAGES], w_empty[CS_MAX_STAGES], acc_full[2],
+      acc_free[2];
+  __shared__ uint32_t tmem_base_s;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ngroups = p.ngroups;
+  const int ncols = p.grp[0].ncols;          // all groups of a layer have the same width (pack_tc_layer)
+  const TcSrc& S = p.src[0];
+  const int planes = S.planes, taps = S.taps, cp = planes * 8;
+  const uint32_t lbo_a = (uint32_t)S.rows * 16;
+  const uint32_t a_bytes = (uint32_t)planes * lbo_a;
+  const uint32_t w_stage_bytes = (uint32_t)(kb_stage / 8) * ncols * 16;
+  uint8_t* sA = smem;                                   // [na][planes][rows][8]
+  uint8_t* sW = smem + (size_t)na * a_bytes;            // ring of [kb/8 planes][ncols][8] stages
+  uint8_t* sOnes = sW + (size_t)nst * w_stage_bytes;    // [128 rows][8]: K0 = K1 = 1 (A of the bias MMA)
+  uint8_t* sBias = sOnes + 128 * 16;                    // [group][ncols][8]: K0 / K1 = bias hi / lo (B of the bias MMA)
+  uint8_t* sZero = sBias + (size_t)ngroups * ncols * 16;   // max(128, ncols) zero rows: second K-plane of both
+  const uint32_t acc_stride = ncols <= 32 ? 32 : ncols <= 64 ? 64 : ncols <= 128 ? 128 : 256;
+  const int n_units = n_tiles * batch;
+  const int kchunks = (cp + kb_stage - 1) / kb_stage;
+  const int stages_per_group = taps * kchunks;
+
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&a_full[i], 1);
+      mbar_init(&a_free[i], 1);
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_free[i], EPI_THREADS);
+    }
+    for (int s = 0; s < nst; ++s) {
+      mbar_init(&w_full[s], 1);
+      mbar_init(&w_empty[s], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc(&tmem_base_s, 2 * acc_stride);
+  for (int e = tid; e < 128; e += NTS) *reinterpret_cast<uint4*>(sOnes + e * 16) = make_uint4(0x3F803F80u, 0u, 0u, 0u);
+  for (int g = 0; g < ngroups; ++g)
+    for (int c = tid; c < ncols; c += NTS) {
+      const float bv = p.grp[g].bias[c];
+      const __nv_bfloat16 hi = __float2bfloat16(bv), lo = __float2bfloat16(bv - __bfloat162float(hi));
+      *reinterpret_cast<uint4*>(sBias + ((size_t)g * ncols + c) * 16) =
+          make_uint4((uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16), 0u, 0u, 0u);
+    }
+  for (int e = tid; e < (ncols > 128 ? ncols : 128); e += NTS)
+    *reinterpret_cast<uint4*>(sZero + e * 16) = make_uint4(0u, 0u, 0u, 0u);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = tmem_base_s;
+  pdl_launch_dependents();
+
+  constexpr int PRODUCER2 = NT / 32;   // the extra warp: odd weight stages
+  if (warp == 0 || warp == PRODUCER2) {
+    if (elect_one()) {
+      const uint32_t mine = warp == 0 ? 0 : 1;
+      Tracer tr = make_tracer(p.trace, warp == 0 ? 0 : 11, true);
+      tr(9);
+      // Weights are written by no kernel: the ring starts filling before the previous kernel has drained.
+      uint32_t it = 0;
+      int i = 0;
+      bool waited = false;
+      for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++i) {
+        if (warp == 0) {   // this unit's activation tile: one bulk copy per 8-channel plane
+          if (!waited) {
+            pdl_wait();    // the previous kernel's output is complete from here on
+            waited = true;
+          }
+          const int ab = i % na;
+          if (i >= na) mbar_wait(&a_free[ab], ((i / na) - 1) & 1);
+          const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
+          const __nv_bfloat16* gx = S.x + (int64_t)b * S.batch_stride + (int64_t)(S.row_base + t0) * 8;
+          mbar_expect_tx(&a_full[ab], a_bytes);
+          for (int pl = 0; pl < planes; ++pl)
+            bulk_g2s(sA + (size_t)ab * a_bytes + (size_t)pl * lbo_a, gx + (int64_t)pl * S.plane_rows * 8, lbo_a,
+                     &a_full[ab]);
+          tr(10);
+        }
+        for (int g = 0; g < ngroups; ++g) {
+          const __nv_bfloat16* gw = p.grp[g].w;
+          for (int j = 0; j < taps; ++j)
+            for (int c0 = 0; c0 < cp; c0 += kb_stage, ++it) {
+              const int kb = min(kb_stage, cp - c0);
+              if ((it & 1) == mine) {
+                const int st = it % nst;
+                mbar_wait(&w_empty[st], ((it / nst) & 1) ^ 1);
+                tr(11);
+                const uint32_t bytes = (uint32_t)(kb / 8) * ncols * 16;
+                mbar_expect_tx(&w_full[st], bytes);
+                bulk_g2s(sW + (size_t)st * w_stage_bytes, gw, bytes, &w_full[st]);
+                tr(12);
+              }
+              gw += (int64_t)kb * ncols;
+            }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    pdl_wait();
+    const bool leader = elect_one() != 0;
+    const uint32_t idesc = make_idesc_bf16(TC_TILE_M, ncols);
+    const uint32_t lbo_b = (uint32_t)ncols * 16;
+    const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, lbo_b, 128);
+    const uint32_t w_base = smem_u32(sW), a_base0 = smem_u32(sA);
+    const uint64_t ones_desc = make_desc(smem_u32(sOnes), smem_u32(sZero) - smem_u32(sOnes), 128);
+    uint32_t it = 0, gg = 0;
+    int i = 0;
+    Tracer tr = make_tracer(p.trace, 1, leader);
+    tr(19);
+    for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++i) {
+      const int ab = i % na;
+      mbar_wait(&a_full[ab], (i / na) & 1);
+      tc_fence_after();
+      tr(18);
+      const uint32_t a_base = a_base0 + (uint32_t)ab * a_bytes;
+      for (int g = 0; g < ngroups; ++g, ++gg) {
+        const int buf = gg & 1;
+        mbar_wait(&acc_free[buf], (gg >> 1) & 1);   // drained by the epilogue
+        tc_fence_after();
+        tr(20);
+        const uint32_t d = tbase + buf * acc_stride;
+        if (leader) {   // D <- bias (overwrites)
+          const uint32_t ba = smem_u32(sBias + (size_t)g * ncols * 16);
+          umma_bf16(d, ones_desc, make_desc(ba, smem_u32(sZero) - ba, 128), idesc, 0);
+        }
+        __syncwarp();
+        for (int j = 0; j < taps; ++j) {
+          const uint32_t a_tap = a_base + (uint32_t)S.tap_row[j] * 16;
+          for (int c0 = 0; c0 < cp; c0 += kb_stage, ++it) {
+            const int kb = min(kb_stage, cp - c0);
+            const int st = it % nst;
+            mbar_wait(&w_full[st], (it / nst) & 1);
+            tc_fence_after();
+            tr(22);
+            if (leader) {
+              uint32_t a_lo = (a_tap + (uint32_t)(c0 >> 3) * lbo_a) >> 4;
+              uint32_t b_lo = (w_base + (uint32_t)st * w_stage_bytes) >> 4;
+              for (int kk = 0; kk < kb / 16; ++kk) {
+                umma_bf16(d, a_tmpl | a_lo, b_tmpl | b_lo, idesc, 1);
+                a_lo += lbo_a >> 3;   // two planes further, in 16-byte units
+                b_lo += lbo_b >> 3;
+              }
+              umma_commit(&w_empty[st]);
+            }
+            __syncwarp();
+          }
+        }
+        if (leader) {
+          umma_commit(&acc_full[buf]);
+          if (g == ngroups - 1) umma_commit(&a_free[ab]);   // the tile is not read again
+        }
+        __syncwarp();
+        tr(21);
+      }
+    }
+    (void)stages_per_group;
+  } else {
+    pdl_wait();
+    const int q4 = warp & 3, hf = (warp - 2) >> 2;
+    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
+    const int reach = p.margin == 1 ? p.out_halo : 0;
+    mbar_arrive(&acc_free[0]);
+    mbar_arrive(&acc_free[1]);
+    uint32_t gg = 0;
+    Tracer tr = make_tracer(p.trace, warp, lane == 0);
+    tr(29);
+    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+      const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
+      for (int g = 0; g < ngroups; ++g, ++gg) {
+        const int buf = gg & 1;
+        mbar_wait_relaxed(&acc_full[buf], (gg >> 1) & 1);
+        tc_fence_after();
+        tr(30);
+        // interior tile (warp-uniform): every row valid, no output row within reach of a sequence end
+        const bool interior = p.out_mode == 0 && t0 + TC_TILE_M <= p.Lt && t0 * p.up_f - p.up_P > reach &&
+                              (t0 + TC_TILE_M - 1) * p.up_f - p.up_P + p.up_f - 1 < p.out_L - 1 - reach;
+        if (interior) {
+          if (p.out_lrelu) conv_epilogue_fast<true>(p, p.grp[g], trow + buf * acc_stride, q4, hf, lane, t0, b, p.slope);
+          else conv_epilogue_fast<false>(p, p.grp[g], trow + buf * acc_stride, q4, hf, lane, t0, b, p.slope);
+        } else {
+          conv_epilogue<false>(p, p.grp[g], trow + buf * acc_stride, q4, hf, lane, t0, b, nullptr);
+        }
+        tc_fence_before();
+        mbar_arrive(&acc_free[buf]);
+        tr(31);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tbase, 2 * acc_stride);
+}
+
 // ---- layout helpers --------------------------------------------------------------------------------
 __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int pad, __nv_bfloat16* __restrict__ out,
                                 int planes, int plane_rows, int halo) {
@@ -612,11 +895,42 @@ TcLaunchCtx tc_launch_ctx(int device) {
   c.stack_max_grid = env_int("TTSB200_STACK_MAX_GRID", 0);
   c.stack_debug = env_int("TTSB200_STACK_DEBUG", 0);
   c.conv_debug = env_int("TTSB200_CONV_DEBUG", 0);
-  c.conv_persistent = env_int("TTSB200_CONV_PERSISTENT", 1);
+  c.conv_persistent = env_int("TTSB200_CONV_PERSISTENT", 2);
   c.pqmf_direct = getenv("TTSB200_PQMF_DIRECT") ? 1 : 0;
   c.trace_file = getenv("TTSB200_STACK_TRACE");
   return c;
 }
+
+namespace {
+// Geometry of the activation-resident kernel for this launch; nst == 0 = not eligible (two sources, in-kernel
+// LeakyReLU, fp32 output, uneven groups, or a tile that leaves no room for a useful weight ring).
+struct ConvsPlan { int kb, nst, na; size_t smem; };
+constexpr size_t CS_SMEM_MAX = 227 * 1024 - 1024;   // static: barriers
+ConvsPlan convs_plan(const TcConvParams& p) {
+  ConvsPlan r{0, 0, 0, 0};
+  if (p.nsrc != 1 || p.src[0].lrelu || p.out_mode != 0 || (p.src[0].planes & 1)) return r;
+  const int ncols = p.grp[0].ncols;
+  if (ncols > 256 || (size_t)ncols * p.ngroups > CS_MAX_COLS) return r;
+  for (int g = 1; g < p.ngroups; ++g)
+    if (p.grp[g].ncols != ncols) return r;
+  const size_t a = (size_t)p.src[0].planes * p.src[0].rows * 16;
+  // bias-MMA operands: ones plane, every group's bias plane, one zero plane
+  const size_t extra = 128 * 16 + (size_t)p.ngroups * ncols * 16 + (size_t)(ncols > 128 ? ncols : 128) * 16;
+  // widest stage first: a bulk copy costs its issuing warp ~500 cycles whatever its size (ingest_probe.cu), so the
+  // ring wants few large stages; at least three of them, and a second activation buffer when it still fits
+  for (int kb : {64, 32, 16}) {
+    const size_t stage = (size_t)(kb / 8) * ncols * 16;
+    if (a + extra + 3 * stage > CS_SMEM_MAX) continue;
+    r.kb = kb;
+    r.na = (2 * a + extra + 4 * stage <= CS_SMEM_MAX) ? 2 : 1;
+    size_t n = (CS_SMEM_MAX - extra - r.na * a) / stage;
+    r.nst = (int)(n > CS_MAX_STAGES ? CS_MAX_STAGES : n);
+    r.smem = r.na * a + r.nst * stage + extra;
+    return r;
+  }
+  return r;
+}
+}  // namespace
 
 cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCtx& ctx, cudaStream_t stream) {
   TcConvParams p = p_in;
@@ -626,15 +940,29 @@ cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCt
   if (!(attr_done.load(std::memory_order_acquire) & bit)) {
     cudaError_t e = cudaFuncSetAttribute(tc_convp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
     if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(tc_convs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CS_SMEM_MAX);
+    if (e == cudaSuccess)
       e = cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
     if (e != cudaSuccess) return e;
     attr_done.fetch_or(bit, std::memory_order_release);
   }
   p.debug = ctx.conv_debug;
+  if (ctx.conv_persistent == 1) {
+    const ConvsPlan cs = convs_plan(p);
+    if (cs.nst >= 3) {
+      const int n_tiles = ceil_div(p.Lt, TC_TILE_M);
+      const int units = n_tiles * batch;
+      p.trace = trace_begin(ctx.trace_file, stream);
+      const cudaError_t rc = launch_pdl(tc_convs_kernel, dim3(units < ctx.sms ? units : ctx.sms), dim3(NTS), cs.smem,
+                                        stream, p, cs.kb, cs.nst, cs.na, n_tiles, batch);
+      trace_end(ctx.trace_file, p.trace, 1000 + p.trace_id, stream);
+      return rc;
+    }
+  }
   {
     size_t smem = 0;
     const int sms = ctx.sms;
-    const int nslots = ctx.conv_persistent ? convp_slots(p, &smem) : 0;
+    const int nslots = ctx.conv_persistent == 2 ? convp_slots(p, &smem) : 0;
     if (nslots > 0 && p.ngroups <= sms) {
       const int n_tiles = ceil_div(p.Lt, TC_TILE_M);
       int per_group = sms / p.ngroups;

@@ -88,7 +88,7 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
     const int Cin = cfg.in_channels, k = cfg.proj_kernel;
     if (int rc = pack_tc_layer(b16, bb, plan->tc_proj, 1, taps, cin, cfg.base_channels, 1,
                                [&](int, int j, int ci, int, int co) { return w[((size_t)co * Cin + ci) * k + j]; },
-                               [&](int co) { return b[co]; }, true))
+                               [&](int co) { return b[co]; }, plan->ctx.conv_persistent == 2))
       return rc;
     ti += 2;
   }
@@ -105,7 +105,7 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
                                  [&](int, int j, int ci, int ph, int co) {
                                    return w[((size_t)ci * Cout + co) * (2 * f) + ph + f * j];
                                  },
-                                 [&](int co) { return b[co]; }, true))
+                                 [&](int co) { return b[co]; }, plan->ctx.conv_persistent == 2))
         return rc;
       ti += 2;
     }

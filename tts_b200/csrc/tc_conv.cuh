@@ -15,7 +15,9 @@ struct TcLaunchCtx {
   int stack_max_grid = 0;      // TTSB200_STACK_MAX_GRID: test hook, few CTAs so each walks many items
   int stack_debug = 0;         // TTSB200_STACK_DEBUG / TTSB200_CONV_DEBUG: knock-out bits (trace builds only)
   int conv_debug = 0;
-  int conv_persistent = 1;     // TTSB200_CONV_PERSISTENT=0: generic conv kernel everywhere
+  int conv_persistent = 2;     // TTSB200_CONV_PERSISTENT: 2 weights-resident persistent kernel (narrow column groups,
+                               // the default: fastest at cfg2), 1 activation-resident persistent kernel (weights
+                               // streamed, N = 192-256 per MMA; measured 0.321 vs 0.309 ms per step), 0 generic only
   int pqmf_direct = 0;         // TTSB200_PQMF_DIRECT: direct 63-tap synthesis instead of the factorised form
   const char* trace_file = nullptr;   // TTSB200_STACK_TRACE (trace builds only)
 };

@@ -405,6 +405,7 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
     ti += 1;
   }
   plan->hop_generator = hop;
+  plan->ctx = tc_launch_ctx(device);   // before packing: the conv kernel choice sets the column-group widths
   Bf16Builder b16;
   if (int rc = pack_bf16(plan, tensors, bb, b16)) {
     delete plan;
@@ -416,7 +417,6 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
   int prev = 0;
   cudaGetDevice(&prev);
   cudaError_t e = cudaSetDevice(device);
-  if (e == cudaSuccess) plan->ctx = tc_launch_ctx(device);
   if (e == cudaSuccess) e = cudaMalloc(&plan->blob, plan->blob_floats * sizeof(float));
   if (e == cudaSuccess)
     e = cudaMemcpy(plan->blob, bb.data.data(), plan->blob_floats * sizeof(float), cudaMemcpyHostToDevice);
