@@ -102,3 +102,50 @@ def test_dropin_aliases():
         for k in [k for k in sys.modules if k == "TTS" or k.startswith("TTS.")]:
             del sys.modules[k]
         sys.modules.update(saved)
+
+
+REFERENCE_ROOT = "/root/reference"
+
+
+@pytest.mark.skipif(not __import__("os").path.isdir(REFERENCE_ROOT), reason="build container only: needs /root/reference")
+def test_reference_setup_generator_resolves_to_this_package(monkeypatch):
+    """The reference's OWN factory (TTS/vocoder/utils/generic_utils.py:40-94), unmodified, under dropin.install():
+    its module imports matplotlib and TTS.tts.utils.visual at top level (:4-6), neither importable here, so those two
+    names are stubbed in sys.modules; importlib + to_camel + the substring dispatch are the reference's code."""
+    import importlib
+    import sys
+    from tts_b200 import dropin
+
+    saved = {k: v for k, v in sys.modules.items() if k == "TTS" or k.startswith("TTS.") or k.startswith("matplotlib")}
+    for k in saved:
+        monkeypatch.delitem(sys.modules, k, raising=False)
+    monkeypatch.syspath_prepend(REFERENCE_ROOT)
+    mpl = types.ModuleType("matplotlib")
+    mpl.pyplot = types.ModuleType("matplotlib.pyplot")
+    monkeypatch.setitem(sys.modules, "matplotlib", mpl)
+    monkeypatch.setitem(sys.modules, "matplotlib.pyplot", mpl.pyplot)
+    visual = types.ModuleType("TTS.tts.utils.visual")
+    visual.plot_spectrogram = lambda *a, **k: None
+    try:
+        importlib.import_module("TTS.tts.utils")                  # the real (empty) package
+        monkeypatch.setitem(sys.modules, "TTS.tts.utils.visual", visual)
+        dropin.install()
+        ref = importlib.import_module("TTS.vocoder.utils.generic_utils")
+        assert ref.__file__.startswith(REFERENCE_ROOT)            # the reference's file, not ours
+        for name, cls, params in (
+                ("multiband_melgan_generator", MultibandMelganGenerator, {"upsample_factors": [8, 4, 2], "num_res_blocks": 4}),
+                ("melgan_generator", MelganGenerator, {"upsample_factors": [8, 8, 2, 2], "num_res_blocks": 3}),
+                ("fullband_melgan_generator", FullbandMelganGenerator, {"upsample_factors": [2, 8, 2, 2], "num_res_blocks": 4})):
+            c = types.SimpleNamespace(generator_model=name, generator_model_params=params, audio={"num_mels": 80})
+            m = ref.setup_generator(c)
+            assert type(m) is cls and m.upsample_factors == tuple(params["upsample_factors"])
+            assert m.num_res_blocks == params["num_res_blocks"]
+            ours = setup_generator(c)                             # the restated factory agrees key for key
+            assert sorted(m.state_dict()) == sorted(ours.state_dict())
+        from TTS.vocoder.layers.pqmf import PQMF as RefPathPQMF
+        assert RefPathPQMF is PQMF
+    finally:
+        dropin.uninstall()
+        for k in [k for k in sys.modules if k == "TTS" or k.startswith("TTS.")]:
+            sys.modules.pop(k, None)
+        sys.modules.update(saved)
