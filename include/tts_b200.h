@@ -179,6 +179,45 @@ TTSB200_API int32_t ttsb200_profile_read(ttsb200_profile* profile, ttsb200_launc
 /* Number of kernels one ttsb200_generator_forward() launches for this shape (bench "gpu_launches"). */
 TTSB200_API int32_t ttsb200_launch_count(const ttsb200_plan* plan, int32_t precision, int32_t skip_pqmf);
 
+/* ---- Mel front-end (the step in front of the vocoder) --------------------------------------
+ * AudioProcessor.melspectrogram of TTS/utils/audio.py:216-222 in one kernel: pre-emphasis (:198-201), centred
+ * reflect-padded STFT with a periodic Hann window (:258-266, librosa.stft), magnitude, mel filterbank (:203-204),
+ * spec_gain * log10(max(1e-5, x)) (:190-191) and range or mean-var normalisation (:106-134).  The constructor
+ * arguments it reads (:15-71): */
+typedef struct ttsb200_mel_config {
+  int32_t sample_rate;
+  int32_t n_fft;          /* fft_size: a power of two in [256, 2048]                                   */
+  int32_t hop_length;
+  int32_t win_length;     /* <= n_fft (audio.py:72)                                                     */
+  int32_t num_mels;       /* <= 128                                                                     */
+  float preemphasis;      /* 0 = none                                                                   */
+  float spec_gain;
+  float ref_level_db;
+  float min_level_db;     /* != 0 when range normalisation is used (audio.py:71)                        */
+  float max_norm;
+  int32_t signal_norm;
+  int32_t symmetric_norm;
+  int32_t clip_norm;
+} ttsb200_mel_config;
+typedef struct ttsb200_mel_plan ttsb200_mel_plan;
+
+/* mel_basis: HOST [num_mels][n_fft/2 + 1] fp32, the matrix AudioProcessor._build_mel_basis returns (:85-93);
+ * window: HOST [win_length] fp32 (scipy.signal.get_window('hann', win_length, fftbins=True));
+ * mean / scale: HOST [num_mels] StandardScaler statistics of a stats_path config (:185-189), or both NULL. */
+TTSB200_API int32_t ttsb200_mel_plan_create(const ttsb200_mel_config* cfg, const float* mel_basis, const float* window,
+                                            const float* mean, const float* scale, int32_t device,
+                                            ttsb200_mel_plan** out_plan);
+TTSB200_API void ttsb200_mel_plan_destroy(ttsb200_mel_plan* plan);
+/* 1 + n_samples / hop_length frames (librosa.stft, center=True). */
+TTSB200_API int64_t ttsb200_mel_frames(const ttsb200_mel_plan* plan, int64_t n_samples);
+/* wav: device [batch][n_samples] fp32 -> out: device [batch][num_mels][frames] fp32 (the vocoder's input layout). */
+TTSB200_API int32_t ttsb200_mel_forward(const ttsb200_mel_plan* plan, const float* wav, int32_t batch, int64_t n_samples,
+                                        float* out, void* stream);
+/* Frame statistics for find_endpoint / trim_silence (audio.py:302-316): for frame f = samples [f*hop, f*hop +
+ * frame_length) clipped to the signal, out[b][f] = {max x, max |x|, mean x^2}; ceil(n_samples / hop) frames. */
+TTSB200_API int32_t ttsb200_frame_stats(const float* wav, int32_t batch, int64_t n_samples, int32_t frame_length,
+                                        int32_t hop, float* out, void* stream);
+
 /* Diagnostics for the roofline denominators MEASURED_PEAKS.json does not carry (bench.py).
  * fp32 FFMA rate of `device` in TFLOP/s (register-resident FMA loop on every SM, CUDA events) — the ceiling of the
  * TTSB200_F32 path; pinned host<->device copy rate in GB/s over `streams` concurrent copies of `bytes` each

@@ -54,6 +54,24 @@ class ForwardArgs(ctypes.Structure):
     ]
 
 
+class MelConfig(ctypes.Structure):
+    _fields_ = [
+        ("sample_rate", ctypes.c_int32),
+        ("n_fft", ctypes.c_int32),
+        ("hop_length", ctypes.c_int32),
+        ("win_length", ctypes.c_int32),
+        ("num_mels", ctypes.c_int32),
+        ("preemphasis", ctypes.c_float),
+        ("spec_gain", ctypes.c_float),
+        ("ref_level_db", ctypes.c_float),
+        ("min_level_db", ctypes.c_float),
+        ("max_norm", ctypes.c_float),
+        ("signal_norm", ctypes.c_int32),
+        ("symmetric_norm", ctypes.c_int32),
+        ("clip_norm", ctypes.c_int32),
+    ]
+
+
 class LaunchRecord(ctypes.Structure):
     _fields_ = [
         ("name", ctypes.c_char_p),
@@ -92,6 +110,15 @@ SYMBOLS = {
     "ttsb200_profile_reset": (None, [ctypes.c_void_p]),
     "ttsb200_profile_read": (ctypes.c_int32, [ctypes.c_void_p, ctypes.POINTER(LaunchRecord), ctypes.c_int32]),
     "ttsb200_launch_count": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32]),
+    "ttsb200_mel_plan_create": (ctypes.c_int32, [ctypes.POINTER(MelConfig), ctypes.c_void_p, ctypes.c_void_p,
+                                                 ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32,
+                                                 ctypes.POINTER(ctypes.c_void_p)]),
+    "ttsb200_mel_plan_destroy": (None, [ctypes.c_void_p]),
+    "ttsb200_mel_frames": (ctypes.c_int64, [ctypes.c_void_p, ctypes.c_int64]),
+    "ttsb200_mel_forward": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64,
+                                             ctypes.c_void_p, ctypes.c_void_p]),
+    "ttsb200_frame_stats": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32,
+                                             ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]),
     "ttsb200_diag_ffma_tflops": (ctypes.c_double, [ctypes.c_int32]),
     "ttsb200_diag_hostlink_gbs": (ctypes.c_double, [ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32]),
 }

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libtts_b200.so")
-SOURCES = ["vocoder.cu", "conv_f32.cu", "pqmf.cu", "conv_bf16_tc.cu", "stack_bf16_tc.cu", "diag.cu"]
+SOURCES = ["vocoder.cu", "conv_f32.cu", "pqmf.cu", "conv_bf16_tc.cu", "stack_bf16_tc.cu", "diag.cu", "mel.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
