@@ -138,6 +138,19 @@ TTSB200_API int32_t ttsb200_layer_shape(const ttsb200_plan* plan, int32_t layer,
 /* generator.inference(mel) / generator.forward(mel): asynchronous on args->stream, device buffers. */
 TTSB200_API int32_t ttsb200_generator_forward(const ttsb200_plan* plan, const ttsb200_forward_args* args);
 
+/* The same forward with NO allocation anywhere on the call: args->workspace / workspace_bytes are ignored and the
+ * scratch is a file-scope `static __device__` array of TTSB200_STATIC_WORKSPACE_BYTES inside the library (every GPU
+ * that loads the library holds those bytes until exit).  For callers that cannot call cudaMalloc: code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it.  No counterpart in the reference.
+ * Shapes whose ttsb200_workspace_bytes() exceeds the array are refused with
+ * TTSB200_ERR_WORKSPACE (the message names both sizes); args->profile must be NULL (a profile creates events).
+ * Every call on a device shares the one array, which keeps the previous call's contents (nothing in it has to start
+ * at zero: each region is written before it is read): calls that overlap on the GPU — two streams, two threads —
+ * race; order them on one stream or with events.  The first call per device resolves the array's address
+ * (cudaGetSymbolAddress); make it outside a graph capture. */
+#define TTSB200_STATIC_WORKSPACE_BYTES (32u << 20)
+TTSB200_API int32_t ttsb200_generator_forward_static(const ttsb200_plan* plan, const ttsb200_forward_args* args);
+
 /* Same with HOST buffers (pageable or pinned): copies mel in, runs, copies the waveform out and
  * synchronises — the call TTS/server/synthesizer.py:153-159 amounts to.  Uses plan-owned device
  * and pinned staging buffers (serialised by a mutex). */

@@ -60,6 +60,7 @@ def test_argument_validation_without_gpu():
     with pytest.raises(RuntimeError):
         _lib.check(lib.ttsb200_generator_forward(None, None))
     assert lib.ttsb200_output_length(None, 1, 0, 0) < 0
+    assert lib.ttsb200_generator_forward_static(None, None) < 0
 
 
 def test_sass_is_sm100a_only():

@@ -12,6 +12,7 @@ ABI_VERSION = 2
 MAX_STAGES = 8
 F32, BF16 = 0, 1
 OUT_F32, OUT_F16 = 0, 1
+STATIC_WORKSPACE_BYTES = 32 << 20   # TTSB200_STATIC_WORKSPACE_BYTES
 PRECISIONS = {"fp32": F32, "f32": F32, "float32": F32, "bf16": BF16, "bfloat16": BF16}
 
 
@@ -97,6 +98,7 @@ SYMBOLS = {
     "ttsb200_layer_shape": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int64)]),
     "ttsb200_generator_forward": (ctypes.c_int32, [ctypes.c_void_p, ctypes.POINTER(ForwardArgs)]),
+    "ttsb200_generator_forward_static": (ctypes.c_int32, [ctypes.c_void_p, ctypes.POINTER(ForwardArgs)]),
     "ttsb200_generator_forward_host": (ctypes.c_int32, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32,
                                                         ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                                         ctypes.c_void_p]),

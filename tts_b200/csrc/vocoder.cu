@@ -8,6 +8,11 @@
 
 #include "plan.h"
 
+// Scratch of ttsb200_generator_forward_static(): lives in the module image, so that entry point never allocates.
+// One array per GPU that loads the library, held until exit.  In host code this name is only a handle for
+// cudaGetSymbolAddress — never a device address.
+static __device__ __align__(256) unsigned char g_static_workspace[TTSB200_STATIC_WORKSPACE_BYTES];
+
 namespace ttsb {
 
 static thread_local std::string g_last_error;
@@ -523,6 +528,48 @@ int32_t ttsb200_generator_forward(const ttsb200_plan* plan, const ttsb200_forwar
     case TTSB200_BF16: return forward_bf16(plan, a);
     default: return fail(TTSB200_ERR_INVALID, "unknown precision");
   }
+}
+
+int32_t ttsb200_generator_forward_static(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
+  if (!plan || !a) return fail(TTSB200_ERR_INVALID, "NULL argument");
+  if (a->profile)   // a profile creates CUDA events on demand
+    return fail(TTSB200_ERR_INVALID, "ttsb200_generator_forward_static takes no profile (it would allocate events)");
+  if (plan->ctx.trace_file)
+    return fail(TTSB200_ERR_INVALID, "ttsb200_generator_forward_static: the plan was created with a trace file (debug builds allocate)");
+  if (a->batch <= 0 || a->frames <= 0 || a->pad < 0)
+    return fail(TTSB200_ERR_INVALID, "batch/frames must be positive, pad >= 0");
+  const int64_t need = ttsb200_workspace_bytes(plan, a->batch, a->frames, a->pad, a->precision);
+  if (need < 0) return (int32_t)need;
+  if ((uint64_t)need > (uint64_t)TTSB200_STATIC_WORKSPACE_BYTES)
+    return fail(TTSB200_ERR_WORKSPACE, "ttsb200_generator_forward_static: this shape needs " + std::to_string(need) +
+                                           " bytes of scratch, the static array holds " +
+                                           std::to_string((uint64_t)TTSB200_STATIC_WORKSPACE_BYTES) +
+                                           " (TTSB200_STATIC_WORKSPACE_BYTES); use ttsb200_generator_forward with a caller workspace");
+  // Set-up, once per device, with that device current: the array's device address on the plan's GPU.
+  constexpr int MAX_DEVICES = 64;
+  static std::mutex mu;
+  static void* addr[MAX_DEVICES] = {};
+  if (plan->device < 0 || plan->device >= MAX_DEVICES) return fail(TTSB200_ERR_INVALID, "device index out of range");
+  void* ws = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[plan->device]) {
+      int prev = 0;
+      TTSB_CUDA(cudaGetDevice(&prev));
+      if (prev != plan->device) TTSB_CUDA(cudaSetDevice(plan->device));
+      void* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&p, g_static_workspace);
+      if (prev != plan->device) cudaSetDevice(prev);
+      if (e != cudaSuccess || !p)
+        return fail(TTSB200_ERR_CUDA, std::string("cudaGetSymbolAddress(g_static_workspace): ") + cudaGetErrorString(e));
+      addr[plan->device] = p;
+    }
+    ws = addr[plan->device];
+  }
+  ttsb200_forward_args b = *a;
+  b.workspace = ws;
+  b.workspace_bytes = (size_t)TTSB200_STATIC_WORKSPACE_BYTES;
+  return ttsb200_generator_forward(plan, &b);
 }
 
 int32_t ttsb200_generator_forward_host(ttsb200_plan* plan, const float* mel_host, int32_t batch, int32_t frames,
