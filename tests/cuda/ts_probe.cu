@@ -62,7 +62,8 @@ __global__ void ts_kernel(const __nv_bfloat16* A, const __nv_bfloat16* B, float*
   for (int c = 0; c < N; c += 16) {
     float v[16];
     tmem_ld16(tlane + d_col + c, v);
-    for (int i = 0; i < 16; ++i) D[(size_t)row * N + c + i] = v[i];
+    for (int i = 0; i < 16; ++i)
+      if (c + i < N) D[(size_t)row * N + c + i] = v[i];   // N = 24: M = 128 with N a multiple of 8, not 16
   }
   tc_fence_before();
   __syncthreads();
@@ -131,7 +132,8 @@ static float bf16r(float x) { return __bfloat162float(__float2bfloat16(x)); }
 int main() {
   int fails = 0;
   const int cfgs[][4] = {{96, 96, 0, 256}, {96, 96, 96, 0}, {48, 48, 200, 0}, {32, 32, 0, 480}, {192, 192, 256, 0},
-                         {96, 16, 96, 0}, {256, 64, 256, 0}};
+                         {96, 16, 96, 0}, {256, 64, 256, 0},
+                         {24, 32, 64, 0}, {40, 48, 200, 0}};
   for (auto& c : cfgs) {
     const int N = c[0], K = c[1], a_col = c[2], d_col = c[3];
     std::vector<__nv_bfloat16> hA(128 * K), hB(K * N);
@@ -180,7 +182,7 @@ int main() {
   long long* dC;
   cudaMalloc(&dC, 8 * 148);
   cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  const int Ns[] = {32, 48, 96, 128, 192, 256};
+  const int Ns[] = {16, 24, 32, 48, 96, 128, 192, 256};
   for (int mode = 0; mode < 2; ++mode)
     for (int N : Ns)
       for (int nacc : {1, 2}) {

@@ -62,6 +62,8 @@ struct ttsb200_plan {
   size_t blob_floats = 0;
   ttsb::ConvF32 proj, head;
   ttsb::TcLayer tc_proj, tc_head;
+  size_t head_ts_off = 0;           // fused-head operand [cp/8][head_ts_n][8] (taps packed on N), bf16-element offset
+  int head_ts_n = 0;                // its GEMM columns; 0 = this head shape has no fused form
   __nv_bfloat16* blob16 = nullptr;  // all BF16 weights (UMMA canonical K-major layout)
   size_t blob16_elems = 0;
   int halo = 8;                     // margin rows either side of every canonical activation plane

@@ -145,6 +145,18 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
                                [&](int, int j, int ci, int, int co) { return w[((size_t)co * clast + ci) * k + j]; },
                                [&](int co) { return b[co]; }))
       return rc;
+    // Operand of the head fused into the last stack kernel (stack_bf16_tc.cu, TAIL = 1): taps packed on N, column
+    // j * out + c = tap j of output channel c, K-major [cp/8][n][8].
+    if (k == 7 && (cfg.out_channels == 1 || cfg.out_channels == 4)) {
+      const int cp = pad16(clast), n = pad16(k * cfg.out_channels);
+      plan->head_ts_n = n;
+      plan->head_ts_off = b16.alloc((size_t)cp * n);
+      for (int ci = 0; ci < clast; ++ci)
+        for (int j = 0; j < k; ++j)
+          for (int c = 0; c < cfg.out_channels; ++c)
+            b16.data[plan->head_ts_off + ((size_t)(ci >> 3) * n + j * cfg.out_channels + c) * 8 + (ci & 7)] =
+                __float2bfloat16(w[((size_t)c * clast + ci) * k + j]);
+    }
   }
   const int half = (cfg.res_kernel - 1) / 2;
   int sum_d = 0;
@@ -165,10 +177,11 @@ TcStackParams stack_tiling(const ttsb200_plan* plan, int s, bool with_head = fal
   for (int bi = 0; bi < q.nblocks; ++bi) q.dil[bi] = plan->stages[s].blocks[bi].dilation;
   if (with_head) {
     const TcGroupPlan& g = plan->tc_head.groups[0];
-    q.head_w = plan->blob16 + g.w_off;
+    q.head_w = plan->blob16 + plan->head_ts_off;
     q.head_b = plan->blob + g.bias_off;
     q.head_taps = cfg.proj_kernel;
     q.head_ch = cfg.out_channels;
+    q.head_n = plan->head_ts_n;
   }
   if (with_up) {   // the next stage's ConvTranspose1d rides on this stack
     const StagePlan& nx = plan->stages[s + 1];
@@ -190,13 +203,12 @@ bool up_fusable(const ttsb200_plan* plan, int s) {
   if (stack_tiling(plan, s + 1).kt == 0) return false;
   return stack_tiling(plan, s, false, true).kt > 0;
 }
-// The head rides on the last stage's fused kernel when that kernel exists, the head fits its N = 16 tile and
+// The head rides on the last stage's fused kernel when that kernel exists, the head has a packed-tap operand and
 // no per-layer taps were asked for (the stack output is then never materialised).
 bool head_fusable(const ttsb200_plan* plan) {
   const ttsb200_generator_config& cfg = plan->cfg;
   const int s = cfg.n_stages - 1;
-  return cfg.out_channels <= 16 && plan->tc_head.groups.size() == 1 && plan->tc_head.groups[0].ncols == 16 &&
-         stack_tiling(plan, s, true).kt > 0;
+  return plan->head_ts_n > 0 && plan->tc_head.groups.size() == 1 && stack_tiling(plan, s, true).kt > 0;
 }
 
 struct CanonDims {

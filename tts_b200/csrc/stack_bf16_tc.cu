@@ -71,6 +71,7 @@ struct Bars {
   uint64_t w1_full[TC_STACK_MAX_BLOCKS], w2_full[TC_STACK_MAX_BLOCKS], w1_free, w2_free, wh_full;
   uint64_t xa_ready[MAX_KT], xr_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
   uint64_t ring_full[RING_MAX_SLOTS], ring_empty[RING_MAX_SLOTS];
+  uint64_t edge[4 * MAX_KT];   // fused head: warp w's first / last three accumulator rows are in the edge buffer
 };
 
 // TAIL: what follows the last block — 0 the stack output is stored, 1 fused output head, 2 fused transposed conv
@@ -135,14 +136,16 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   uint8_t* sXA = smem;
   uint8_t* sW = smem + 2 * xa_bytes;   // [set][W1 | W2S]
   uint8_t* sWH = sW + (RING ? (size_t)wsets * SLOT_BYTES : (size_t)wsets * (W1_BYTES + W2_BYTES));   // head weights
-  const uint32_t wh_bytes = head ? (uint32_t)p.head_taps * CP * 16 * 2 : 0;
+  const uint32_t wh_bytes = head ? (uint32_t)CP * p.head_n * 2 : 0;
   // Bias operands (B of the bias MMAs): per block {b1, b2 + bs} as [CP rows x 16 B] planes (K-rows 0/1 = hi/lo), the
   // fused tail's bias, and one all-zero plane every descriptor points its second K-plane at (LBO = zero - start).
-  const int tail_n = head ? 16 : up ? p.up_n : 0;
+  const int tail_n = up ? p.up_n : 0;   // the head adds its bias in the epilogue
   uint8_t* sB = sWH + (head ? wh_bytes : (up && p.up_mode == 1) ? up_bytes : 0);
   uint8_t* sBtail = sB + (size_t)nb * 2 * CP * 16;
   uint8_t* sBzero = sBtail + (size_t)tail_n * 16;
   const uint32_t bzero = smem_u32(sBzero);
+  // fused head: per epilogue warp, its first and last three accumulator rows (6 x 32 fp32) for the neighbouring warps
+  float* sEdge = reinterpret_cast<float*>(sBzero + (size_t)(CP > tail_n ? CP : tail_n) * 16);
   auto bias_desc = [&](const uint8_t* bp) {
     const uint32_t a = smem_u32(bp);
     return make_desc(a, bzero - a, 128);
@@ -166,6 +169,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       mbar_init(&bars.ring_full[i], 1);
       mbar_init(&bars.ring_empty[i], 1);
     }
+    for (int i = 0; i < 4 * MAX_KT; ++i) mbar_init(&bars.edge[i], 32);
     for (int t = 0; t < KT; ++t) {
       mbar_init(&bars.xa_ready[t], GROUP_THREADS);
       mbar_init(&bars.xr_ready[t], GROUP_THREADS);
@@ -194,7 +198,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       const int blk = e / (2 * CP), r = e - blk * 2 * CP;
       put_bias(sB + (size_t)e * 16, r < CP ? p.b1[blk][r] : p.b2s[blk][r - CP]);
     }
-    for (int e = tid; e < tail_n; e += NT) put_bias(sBtail + (size_t)e * 16, head ? p.head_b[e] : p.up_b[e]);
+    for (int e = tid; e < tail_n; e += NT) put_bias(sBtail + (size_t)e * 16, p.up_b[e]);
     const int zn = CP > tail_n ? CP : tail_n;
     for (int e = tid; e < zn; e += NT) *reinterpret_cast<uint4*>(sBzero + (size_t)e * 16) = make_uint4(0u, 0u, 0u, 0u);
     fence_proxy_async();   // the MMAs read these through the async proxy
@@ -421,7 +425,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         if (leader) {
           umma_commit(&bars.d1_full[KT - 1]);
           if (wsets == 1) umma_commit(&bars.w1_free);
-          if (blk == nb - 1 && !tail) umma_commit(&bars.x_free[buf]);   // XA is not read again for this item
+          // XA is not read again for this item (the fused head reads lrelu(x_out) from TMEM)
+          if (blk == nb - 1 && (!tail || head)) umma_commit(&bars.x_free[buf]);
         }
         __syncwarp();
         ++n_xa;
@@ -494,33 +499,31 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         __syncwarp();
       }
       if (head) {
-        // ---- fused output head: D1[t][0:16] = sum_tap lrelu(x_out)[rows + tap - hh] Wh[tap]^T   (N = 16)
-        constexpr uint32_t idesc_h = make_idesc_bf16(128, 16);
-        const uint64_t bh_tmpl = make_desc(0, 16 * 16, 128);
+        // ---- fused output head, taps packed on N: P[t][j * ch + c] = sum_ci lrelu(x_out)[t][ci] Wh[c][ci][j], ONE
+        // K = CP round per tile with A = lrelu(x_out) in TMEM (XR[t], written by the last epilogue 2): KS MMAs instead
+        // of taps * KS shared-memory-read-bound N = 16 MMAs (34 % of this kernel's tensor time before).  The tap
+        // shifts move to the output side: y[t][c] = sum_j P[t + j - hh][j * ch + c], summed by the epilogue.
+        const uint32_t idesc_h = make_idesc_bf16(128, p.head_n);
+        const uint32_t lbo_h = (uint32_t)p.head_n * 16;
+        const uint64_t bh_tmpl = make_desc(0, lbo_h, 128);
         const uint32_t wh = smem_u32(sWH);
         if (it == 0) mbar_wait(&bars.wh_full, 0);
 #pragma unroll 1
         for (int t = 0; t < KT; ++t) {
-          if (t == 0) mbar_wait(&bars.xa_ready[0], n_xa & 1);
-          if (t + 1 < KT) mbar_wait(&bars.xa_ready[t + 1], n_xa & 1);
+          mbar_wait(&bars.xa_ready[t], n_xa & 1);
           tc_fence_after();
+          tr(150 + t);
+          const uint32_t tcol = tbase + t * TCOLS;
           if (leader) {
-            umma_bf16_ts(tbase + t * TCOLS, tbase + ONES_COL, bias_desc(sBtail), idesc_h, 0);   // head accumulator <- bias
-            for (int j = 0; j < p.head_taps; ++j) {
-              const uint32_t a_row = xa + (uint32_t)(G + t * 128 + j - hh) * 16;
-              const uint32_t w_tap = wh + (uint32_t)j * (CP * 16 * 2);
 #pragma unroll
-              for (int kk = 0; kk < KS; ++kk)
-                umma_bf16(tbase + t * TCOLS, a_tmpl | (uint64_t)((a_row + 2 * kk * lbo_a) >> 4),
-                          bh_tmpl | (uint64_t)((w_tap + 2 * kk * 256) >> 4), idesc_h, 1);
-            }
+            for (int kk = 0; kk < KS; ++kk)
+              umma_bf16_ts(tcol, tcol + 2 * CP + 8 * kk, bh_tmpl | (uint64_t)((wh + 2 * kk * lbo_h) >> 4), idesc_h,
+                           kk > 0);
             umma_commit(&bars.d1_full[t]);
           }
           __syncwarp();
         }
         ++n_xa;
-        if (leader) umma_commit(&bars.x_free[buf]);
-        __syncwarp();
       }
       if (up) {
         // ---- fused transposed conv of the next stage: D[t][0:N] = a[q] Wu[0]^T + a[q-1] Wu[1]^T, a = lrelu(x_out)
@@ -624,6 +627,12 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         }
       }
     };
+    float head_bias[4] = {0.f, 0.f, 0.f, 0.f};   // fused head: its bias, read once (an L2 round trip per item otherwise)
+    if (head) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (c < p.head_ch) head_bias[c] = __ldg(p.head_b + c);
+    }
     bool staged = false;   // the current item's first prologue half already ran (during the previous item's tail)
 
     int gb = 0;
@@ -885,11 +894,12 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) a[i] = DBG(32) ? w[i] : lrelu_bf16x2(w[i], slope2);
             tr(224);
-            if (last && up) put_xa_up(a);
+            if (last && head) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, a);   // A operand of the fused head (TMEM)
+            else if (last && up) put_xa_up(a);
             else put_xa(a);
             tr(225);
             tmem_wait_st();
-            if (!DBG(8)) fence_proxy_async();
+            if (!DBG(8) && !(last && head)) fence_proxy_async();
             tr(226);
             tc_fence_before();
             mbar_arrive(&bars.xa_ready[t]);
@@ -945,19 +955,72 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         if (staged) stage_item(it + 1);
       }
       if (head) {
-        // ---- epilogue 3: tanh of the head accumulator -> fp32 [batch][head_ch][L]
-        mbar_wait(&bars.d1_full[t], n_d1++ & 1);
-        tc_fence_after();
-        uint32_t v[16];
-        tmem_ld16_nw(tlane, v);
-        tmem_wait_ld();
-        const int tau = g0 + t * 128 + m;
-        if (tau >= chain * V && tau < (chain + 1) * V && tau < L) {
-          float* of = p.head_out + (int64_t)b * p.head_ch * L + tau;
+        // ---- epilogue 3: y[t][c] = bias[c] + sum_j P[reflect(t + j - 3)][j * ch + c], tanh -> fp32 [batch][ch][L].
+        // Thread = row: the shifted rows come from other lanes by shuffle; rows that belong to a neighbouring warp
+        // (first / last three lanes) come from that warp's edge rows in shared memory.  ReflectionPad1d of the head
+        // (melgan_generator.py:66) is the index map reflect(): its sources are never more than three rows away.
+        auto head_epi = [&](auto ch_c) {
+          constexpr int CH = decltype(ch_c)::value;
+          constexpr int HT = 7, HN = CH == 4 ? 32 : 16;
+          constexpr int LAST_W = 4 * KT - 1;
+          const int wic = t * 4 + q4;                       // this warp's position in the chain (32 rows each)
+          float* eb = sEdge + wic * (6 * 32);
+          mbar_wait(&bars.d1_full[t], n_d1++ & 1);
+          tc_fence_after();
+          tr(240);
+          uint32_t v[HN];
+          tmem_ld_nw<HN>(tlane, v);
+          tmem_wait_ld();
+          tr(241);
+          if (lane < 3 || lane >= 29) {
+            float4* dst = reinterpret_cast<float4*>(eb + (lane < 3 ? lane : lane - 26) * 32);
 #pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (i < p.head_ch) of[(int64_t)i * L] = tanh_fast(__uint_as_float(v[i]));
-        }
+            for (int i = 0; i < (HT * CH + 3) / 4; ++i)
+              dst[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
+                                   __uint_as_float(v[4 * i + 3]));
+          }
+          mbar_arrive(&bars.edge[wic]);                     // release: the rows above are visible to the waiters
+          const int tau = g0 + t * 128 + m;
+          const bool own = tau >= chain * V && tau < (chain + 1) * V && tau < L;
+          float y[CH];
+#pragma unroll
+          for (int c = 0; c < CH; ++c) y[c] = head_bias[c];
+          int sl[HT];                                       // source lane of tap j (outside [0, 32): a neighbour's row)
+#pragma unroll
+          for (int j = 0; j < HT; ++j) {
+            int sr = tau + j - 3;
+            sr = sr < 0 ? -sr : sr;
+            sr = sr >= L ? 2 * (L - 1) - sr : sr;
+            sl[j] = lane + (sr - tau);
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+              const float sv = __shfl_sync(0xffffffffu, __uint_as_float(v[j * CH + c]), sl[j] & 31);
+              if ((unsigned)sl[j] < 32u) y[c] += sv;
+            }
+          }
+          tr(243);
+          if (wic > 0) mbar_wait(&bars.edge[wic - 1], it & 1);
+          if (wic < LAST_W) mbar_wait(&bars.edge[wic + 1], it & 1);
+          tr(244);
+          if (own) {
+#pragma unroll
+            for (int j = 0; j < HT; ++j) {
+              const float* nb = nullptr;
+              if (sl[j] < 0 && wic > 0) nb = eb - 6 * 32 + (sl[j] + 6) * 32 + j * CH;          // rows 29..31 of warp wic - 1
+              else if (sl[j] >= 32 && wic < LAST_W) nb = eb + 6 * 32 + (sl[j] - 32) * 32 + j * CH;   // rows 0..2 of wic + 1
+              if (nb) {
+#pragma unroll
+                for (int c = 0; c < CH; ++c) y[c] += nb[c];
+              }
+            }
+            float* of = p.head_out + (int64_t)b * CH * L + tau;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) of[(int64_t)c * L] = tanh_fast(y[c]);
+          }
+        };
+        if (p.head_ch == 4) head_epi(std::integral_constant<int, 4>{});
+        else head_epi(std::integral_constant<int, 1>{});
+        tr(245);
       }
       if (up) {
         // ---- epilogue 3: transposed-conv accumulator -> next stage's input; GEMM row q holds output rows
@@ -1017,9 +1080,14 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
 constexpr size_t SMEM_MAX = 227 * 1024 - 8 * 1024;   // static: barriers, TMEM base, ring mode's fp32 bias rows (6 KB)
 
 // Bias operands of the bias MMAs: {b1, b2 + bs} per block and the fused tail's bias as [n x 16 B] planes, one zero plane.
+// Fused head: packed weights [cp/8][head_n][8] + per epilogue warp six accumulator rows of 32 fp32 (edge exchange).
+size_t head_smem_bytes(const TcStackParams& p) {
+  return p.head_w ? (size_t)p.cp * p.head_n * 2 + (size_t)4 * tc_stack_kt(p.cp) * 6 * 32 * 4 : 0;
+}
+
 size_t bias_smem_bytes(const TcStackParams& p) {
   if (p.cp > 96) return 0;   // ring mode pre-loads its accumulators instead
-  const size_t tail_n = p.head_w ? 16 : p.up_w ? (size_t)p.up_n : 0;
+  const size_t tail_n = p.up_w ? (size_t)p.up_n : 0;
   return ((size_t)p.nblocks * 2 * p.cp + tail_n + std::max<size_t>(p.cp, tail_n)) * 16;
 }
 
@@ -1083,7 +1151,9 @@ bool tc_stack_configure(TcStackParams& p) {
   }
   p.guard = (dmax + 7) / 8 * 8;
   const bool head = p.head_w != nullptr;
-  if (head && (p.cp > 64 || p.head_taps < 1 || p.head_taps > TC_MAX_TAPS || p.head_taps % 2 == 0 || p.head_ch > 16))
+  // fused head: 7 taps x {1, 4} channels packed on N (the epilogue's shuffle sum is written for those shapes)
+  if (head && (p.cp > 64 || p.head_taps != 7 || (p.head_ch != 1 && p.head_ch != 4) ||
+               p.head_n != (p.head_ch == 4 ? 32 : 16)))
     return false;
   const bool up = p.up_w != nullptr;
   if (up) {
@@ -1099,7 +1169,7 @@ bool tc_stack_configure(TcStackParams& p) {
   if (p.kt * 128 - 2 * (p.sum_d + hh) < 32 || p.guard + p.sum_d + hh > 127) return false;
   const size_t xa = 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;
   const size_t wset = (size_t)(TAPS + 2) * p.cp * p.cp * 2;
-  const size_t wh = (head ? (size_t)p.head_taps * p.cp * 16 * 2 : 0) + bias_smem_bytes(p);
+  const size_t wh = head_smem_bytes(p) + bias_smem_bytes(p);
   // two CTAs per SM when the TMEM footprint allows it: each then gets half of the shared memory
   const size_t budget = tc_stack_ctas_per_sm(p.cp) == 2 ? SMEM_MAX / 2 - 1024 : SMEM_MAX;
   if (p.cp > 96) {   // ring mode: w_sets = number of [RING_KB x cp] chunk slots
@@ -1132,7 +1202,7 @@ size_t tc_stack_smem_bytes(const TcStackParams& p) {
            bias_smem_bytes(p);
   return bias_smem_bytes(p) + 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 +
          (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
-         (p.head_w ? (size_t)p.head_taps * p.cp * 16 * 2 : 0) +
+         head_smem_bytes(p) +
          (p.up_w && p.up_mode == 1 ? (size_t)2 * p.cp * p.up_n * 2 : 0);
 }
 

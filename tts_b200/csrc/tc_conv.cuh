@@ -113,9 +113,12 @@ struct TcStackParams {
   // Optional fused output head (last stage only, cp <= 64): LeakyReLU -> ReflectionPad1d -> Conv1d(k) -> Tanh
   // (melgan_generator.py:65-77) computed from the stack output while it is still in shared memory; the stack
   // output itself is then never written to HBM.
-  const __nv_bfloat16* head_w;   // [taps][cp/8][16][8]; nullptr = no head, write the canonical stack output
-  const float* head_b;           // [16]
-  int head_taps, head_ch;        // kernel size (odd, <= TC_MAX_TAPS), real output channels (<= 16)
+  // Taps are packed on N: column j * head_ch + c is tap j of output channel c, so one K = cp MMA round with
+  // A = lrelu(x_out) in TMEM gives every tap's partial product and the epilogue sums the shifted rows.
+  const __nv_bfloat16* head_w;   // [cp/8][head_n][8]; nullptr = no head, write the canonical stack output
+  const float* head_b;           // [head_ch]
+  int head_taps, head_ch;        // kernel size (7), real output channels (1 or 4)
+  int head_n;                    // GEMM columns: head_taps * head_ch rounded up to 16
   float* head_out;               // fp32 [batch][head_ch][L]
   // Optional fused ConvTranspose1d of the NEXT stage (melgan_generator.py:47-56): the stack output (activated,
   // still in shared memory) is contracted with the two-tap polyphase weights, y[q f - P + r] = a[q] w[r] +
