@@ -897,6 +897,7 @@ TcLaunchCtx tc_launch_ctx(int device) {
   c.conv_debug = env_int("TTSB200_CONV_DEBUG", 0);
   c.conv_persistent = env_int("TTSB200_CONV_PERSISTENT", 2);
   c.pqmf_direct = getenv("TTSB200_PQMF_DIRECT") ? 1 : 0;
+  c.no_k24 = getenv("TTSB200_NO_K24") ? 1 : 0;
   c.trace_file = getenv("TTSB200_STACK_TRACE");
   return c;
 }

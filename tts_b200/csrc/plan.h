@@ -30,6 +30,8 @@ struct TcLayer {
 struct BlockPlan {
   TcLayer tc_conv1, tc_conv2s;  // BF16: dilated k3; fused (1x1 on lrelu(h)) + (1x1 shortcut on x)
   int dilation = 1;
+  bool has_k24 = false;          // 24-channel stage: dilated conv also packed as five K = 16 steps with the bias inside
+  size_t w1_k24_off = 0;         // bf16-element offset of that packing (stack_bf16_tc.cu issue_k24)
   ConvF32 conv1;     // dilated k3                                   melgan.py:20-24
   ConvF32 conv2;     // 1x1 after the second LeakyReLU               melgan.py:26-27
   ConvF32 shortcut;  // 1x1 on the un-activated input                melgan.py:31-34

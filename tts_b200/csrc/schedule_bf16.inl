@@ -124,6 +124,29 @@ int pack_bf16(ttsb200_plan* plan, const float* const* tensors, BlobBuilder& bb, 
                                    [&](int co) { return b1[co]; }))
           return rc;
       }
+      if (C == 24 && k == 3) {
+        // Five-K-step packing of the dilated conv for the fused stack's k24 mode: K-step ks, half h = one 8-channel
+        // plane of one tap, [ks][h][32 columns][8]; the last half is the bias row against the kernel's ones plane
+        // (K-row 0 = bf16 high part, K-row 1 = remainder, as in the bias MMAs).  Sized like the plain packing (3
+        // taps x 32 x 32) so the kernel's loads do not change.
+        static const int tap_of[5][2] = {{0, 0}, {1, 0}, {1, 1}, {2, 2}, {2, -1}};
+        static const int ch_of[5][2] = {{0, 8}, {0, 16}, {8, 16}, {0, 8}, {16, 0}};
+        bp.has_k24 = true;
+        bp.w1_k24_off = b16.alloc((size_t)3 * 32 * 32);
+        for (int ks = 0; ks < 5; ++ks)
+          for (int h = 0; h < 2; ++h)
+            for (int n = 0; n < C; ++n) {
+              __nv_bfloat16* dst = &b16.data[bp.w1_k24_off + ((size_t)(ks * 2 + h) * 32 + n) * 8];
+              if (tap_of[ks][h] < 0) {
+                const __nv_bfloat16 hi = __float2bfloat16(b1[n]);
+                dst[0] = hi;
+                dst[1] = __float2bfloat16(b1[n] - __bfloat162float(hi));
+              } else {
+                for (int e = 0; e < 8; ++e)
+                  dst[e] = __float2bfloat16(w1[((size_t)n * C + ch_of[ks][h] + e) * k + tap_of[ks][h]]);
+              }
+            }
+      }
       {
         const int taps[2] = {1, 1}, cin[2] = {C, C};
         if (int rc = pack_tc_layer(b16, bb, bp.tc_conv2s, 2, taps, cin, C, 1,
@@ -175,6 +198,7 @@ TcStackParams stack_tiling(const ttsb200_plan* plan, int s, bool with_head = fal
   q.res_taps = cfg.res_kernel;
   if (q.nblocks < 1 || q.nblocks > TC_STACK_MAX_BLOCKS) return q;
   for (int bi = 0; bi < q.nblocks; ++bi) q.dil[bi] = plan->stages[s].blocks[bi].dilation;
+  q.k24 = (q.cp == 32 && plan->stages[s].blocks[0].has_k24 && !plan->ctx.no_k24) ? 1 : 0;
   if (with_head) {
     const TcGroupPlan& g = plan->tc_head.groups[0];
     q.head_w = plan->blob16 + plan->head_ts_off;
@@ -369,7 +393,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       q.L = (int)L; q.slope = slope;
       for (int bi = 0; bi < nb; ++bi) {
         const BlockPlan& bp = sp.blocks[bi];
-        q.w1[bi] = Wh + bp.tc_conv1.groups[0].w_off;
+        q.w1[bi] = Wh + (q.k24 ? bp.w1_k24_off : bp.tc_conv1.groups[0].w_off);
         q.w2s[bi] = Wh + bp.tc_conv2s.groups[0].w_off;
         q.b1[bi] = Wf + bp.tc_conv1.groups[0].bias_off;
         q.b2s[bi] = Wf + bp.tc_conv2s.groups[0].bias_off;

@@ -146,6 +146,9 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   const uint32_t bzero = smem_u32(sBzero);
   // fused head: per epilogue warp, its first and last three accumulator rows (6 x 32 fp32) for the neighbouring warps
   float* sEdge = reinterpret_cast<float*>(sBzero + (size_t)(CP > tail_n ? CP : tail_n) * 16);
+  // k24 mode (24 real channels in CP = 32): a constant plane of 128 rows {1, 1, 0 x 6}, the A half of the K-step that
+  // carries the dilated conv's bias.  Above both XA buffers, so the offset from any XA row to it is positive.
+  uint8_t* sOnes = reinterpret_cast<uint8_t*>(sEdge) + (head ? (size_t)4 * KT * 6 * 32 * 4 : 0);
   auto bias_desc = [&](const uint8_t* bp) {
     const uint32_t a = smem_u32(bp);
     return make_desc(a, bzero - a, 128);
@@ -201,6 +204,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     for (int e = tid; e < tail_n; e += NT) put_bias(sBtail + (size_t)e * 16, p.up_b[e]);
     const int zn = CP > tail_n ? CP : tail_n;
     for (int e = tid; e < zn; e += NT) *reinterpret_cast<uint4*>(sBzero + (size_t)e * 16) = make_uint4(0u, 0u, 0u, 0u);
+    if (p.k24)
+      for (int e = tid; e < 128; e += NT) *reinterpret_cast<uint4*>(sOnes + (size_t)e * 16) = make_uint4(0x3F803F80u, 0u, 0u, 0u);
     fence_proxy_async();   // the MMAs read these through the async proxy
   }
   tc_fence_before();
@@ -407,21 +412,53 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             }
           }
         };
+        // k24 mode (CP = 32 carrying 24 real channels, the last MB-MelGAN stage): the 3 x 24 input channels of the three
+        // taps are packed into FIVE K = 16 steps instead of six — (tap0 ch 0-15) (tap1 ch 0-7 | tap0 ch 16-23)
+        // (tap1 ch 8-23) (tap2 ch 0-15) (tap2 ch 16-23 | ones plane x bias row) — the two halves of a K-step being any
+        // two planes whose distance is the descriptor's leading-dimension offset.  The last step also delivers the
+        // bias, so the bias MMA goes too: 5 shared-memory-bound MMAs per tile and block instead of 6 + 1 (these
+        // MMAs' operand reads are what bounds the stage).  Weights: schedule_bf16.inl pack_w1_k24.
+        auto issue_k24 = [&](int t, int half) {   // half 0: steps 0-2 (taps 0, 1; the first overwrites), 1: steps 3-4
+          if (leader) {
+            const uint32_t dcol = tbase + t * TCOLS;
+            const uint32_t r0 = xa + (uint32_t)(G + t * 128 - d) * 16, r1 = r0 + (uint32_t)d * 16, r2 = r1 + (uint32_t)d * 16;
+            auto mma = [&](uint32_t start, uint32_t lbo, int ks, uint32_t acc) {
+              umma_bf16(dcol, make_desc(start, lbo, 128), b_tmpl | (uint64_t)((w1 + ks * 2 * LBO_B) >> 4), idesc, acc);
+            };
+            if (half == 0) {
+              mma(r0, lbo_a, 0, 0);
+              mma(r1, 2 * lbo_a - (uint32_t)d * 16, 1, 1);
+              mma(r1 + lbo_a, lbo_a, 2, 1);
+            } else {
+              mma(r2, lbo_a, 3, 1);
+              mma(r2 + 2 * lbo_a, smem_u32(sOnes) - (r2 + 2 * lbo_a), 4, 1);
+            }
+          }
+        };
 #pragma unroll 1
         for (int t = 0; t < KT; ++t) {
           mbar_wait(&bars.xa_ready[t], n_xa & 1);
           tc_fence_after();
           tr(100 + t);
-          if (t > 0) {
-            issue_taps(t - 1, 2, 3);
-            if (leader) umma_commit(&bars.d1_full[t - 1]);
+          if (p.k24) {
+            if (t > 0) {
+              issue_k24(t - 1, 1);
+              if (leader) umma_commit(&bars.d1_full[t - 1]);
+            }
+            issue_k24(t, 0);
+          } else {
+            if (t > 0) {
+              issue_taps(t - 1, 2, 3);
+              if (leader) umma_commit(&bars.d1_full[t - 1]);
+            }
+            if (leader) umma_bf16_ts(tbase + t * TCOLS, tbase + ONES_COL, b1_desc, idesc, 0);   // D1[t] <- b1 (overwrites)
+            issue_taps(t, 0, 2);
           }
-          if (leader) umma_bf16_ts(tbase + t * TCOLS, tbase + ONES_COL, b1_desc, idesc, 0);   // D1[t] <- b1 (overwrites)
-          issue_taps(t, 0, 2);
           __syncwarp();
           tr(110 + t);
         }
-        issue_taps(KT - 1, 2, 3);
+        if (p.k24) issue_k24(KT - 1, 1);
+        else issue_taps(KT - 1, 2, 3);
         if (leader) {
           umma_commit(&bars.d1_full[KT - 1]);
           if (wsets == 1) umma_commit(&bars.w1_free);
@@ -1087,6 +1124,8 @@ size_t head_smem_bytes(const TcStackParams& p) {
 
 size_t bias_smem_bytes(const TcStackParams& p) {
   if (p.cp > 96) return 0;   // ring mode pre-loads its accumulators instead
+  if (p.k24) return ((size_t)p.nblocks * 2 * p.cp + (p.up_w ? (size_t)p.up_n : 0) +
+                     std::max<size_t>(p.cp, p.up_w ? (size_t)p.up_n : 0)) * 16 + 128 * 16;   // + the ones plane
   const size_t tail_n = p.up_w ? (size_t)p.up_n : 0;
   return ((size_t)p.nblocks * 2 * p.cp + tail_n + std::max<size_t>(p.cp, tail_n)) * 16;
 }

@@ -18,6 +18,7 @@ struct TcLaunchCtx {
   int conv_persistent = 2;     // TTSB200_CONV_PERSISTENT: 2 weights-resident persistent kernel (narrow column groups,
                                // the default: fastest at cfg2), 1 activation-resident persistent kernel (weights
                                // streamed, N = 192-256 per MMA; measured 0.321 vs 0.309 ms per step), 0 generic only
+  int no_k24 = 0;              // TTSB200_NO_K24: keep the six-K-step dilated conv on 24-channel stages (A/B experiments)
   int pqmf_direct = 0;         // TTSB200_PQMF_DIRECT: direct 63-tap synthesis instead of the factorised form
   const char* trace_file = nullptr;   // TTSB200_STACK_TRACE (trace builds only)
 };
@@ -105,6 +106,8 @@ struct TcStackParams {
   const __nv_bfloat16* w2s[TC_STACK_MAX_BLOCKS];  // [2][cp/8][cp][8]  (conv 1x1, shortcut 1x1)
   const float* b1[TC_STACK_MAX_BLOCKS];           // [cp]
   const float* b2s[TC_STACK_MAX_BLOCKS];          // [cp]  conv2.bias + shortcut.bias
+  int k24;                 // cp == 32 carrying 24 real channels: w1[] is the five-K-step packing (bias inside), see
+                           // stack_bf16_tc.cu issue_k24 / schedule_bf16.inl pack_w1_k24
   int kt;                  // 128-row M tiles per work item (fixed per cp: tc_stack_kt)
   int sum_d;               // one-sided receptive field of the stack = sum over blocks of dil
   int guard;               // spare rows either side of the staged tile (>= max dilation reach)
