@@ -427,16 +427,17 @@ constexpr int CP_CHUNK_PLANES = 8;   // 64 channels per activation chunk
 // tests/cuda/ingest_probe.cu) exceeds the chunk's MMA time, so two warps issue alternate chunks.
 // (Measured alternative that lost: ONE 4-D tensor-map copy per chunk, box {8 channels, rows, 8 planes, 1} — the
 // layout's 16-byte inner extent makes the TMA unit fetch 16 bytes per request: convT@6 27.1 -> 29.5 us.)
-constexpr int NTP = NT + 32;
+constexpr int NTP = NT + 64;   // + second activation producer, + the warp that counts finished units (done_out)
 
 __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ TcConvParams p, const int nslots,
                                                        const int n_tiles, const int batch) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bar_w, a_full[CP_MAX_SLOTS], a_empty[CP_MAX_SLOTS], acc_full[2], acc_free[2];
+  __shared__ __align__(8) uint64_t bar_w, a_full[CP_MAX_SLOTS], a_empty[CP_MAX_SLOTS], acc_full[2], acc_free[2], unit_done;
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float s_bias[256];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool follow = p.done_in != nullptr;   // the previous kernel is followed utterance by utterance
   const int ngroups = p.ngroups;
   const TcGroup& G = p.grp[blockIdx.x % ngroups];
   const int ncols = G.ncols;
@@ -462,6 +463,7 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_free[i], EPI_THREADS);
     }
+    mbar_init(&unit_done, EPI_THREADS / 32);
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc(&tmem_base_s, 2 * acc_stride);
@@ -471,21 +473,39 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
   pdl_launch_dependents();
-  if (warp != 0) pdl_wait();   // warp 0 first starts the weight load (weights are written by no kernel)
+  if (warp != 0 && !follow) pdl_wait();   // warp 0 first starts the weight load (weights are written by no kernel)
 
   constexpr int PRODUCER2 = NT / 32;   // the extra warp: odd activation chunks
-  if (warp == 0 || warp == PRODUCER2) {
+  constexpr int SIGNAL_WARP = PRODUCER2 + 1;
+  if (warp == SIGNAL_WARP) {
+    // unit by unit: every epilogue warp has issued its stores -> make them visible device-wide, count the unit for its
+    // utterance (the fence stalls until the stores have drained, so no epilogue warp executes it)
+    if (p.done_out && elect_one()) {
+      int i = 0;
+      for (int u = first; u < n_units; u += stride, ++i) {
+        mbar_wait(&unit_done, i & 1);
+        __threadfence();
+        atomicAdd(p.done_out + u / n_tiles, 1);
+      }
+    }
+  } else if (warp == 0 || warp == PRODUCER2) {
     if (elect_one()) {
       const uint32_t mine = warp == 0 ? 0 : 1;
       if (warp == 0) {
         mbar_expect_tx(&bar_w, (uint32_t)taps * tap_bytes);
         for (int j = 0; j < taps; ++j)
           bulk_g2s(sW + (size_t)j * tap_bytes, G.w + (size_t)j * (tap_bytes / 2), tap_bytes, &bar_w);
-        pdl_wait();
+        if (!follow) pdl_wait();
       }
       uint32_t gc = 0;
+      int ready_b = -1;
       for (int u = first; u < n_units; u += stride) {
         const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
+        if (follow && b > ready_b) {
+          wait_counter(p.done_in + b, p.done_in_target);
+          fence_proxy_async_global();
+          ready_b = b;
+        }
         const __nv_bfloat16* gx = S.x + (int64_t)b * S.batch_stride + (int64_t)(S.row_base + t0) * 8;
         for (int c = 0; c < nchunks; ++c, ++gc) {
           if ((gc & 1) != mine) continue;
@@ -562,6 +582,10 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
       tmem_wait_st();
       tc_fence_before();
       mbar_arrive(&acc_free[buf]);
+      if (p.done_out) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&unit_done);
+      }
       tr(31);
     }
   }
@@ -785,10 +809,12 @@ __global__ void __launch_bounds__(NTS) tc_convs_kernel(const __grid_constant__ T
 
 // ---- layout helpers --------------------------------------------------------------------------------
 __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int pad, __nv_bfloat16* __restrict__ out,
-                                int planes, int plane_rows, int halo) {
+                                int planes, int plane_rows, int halo, int* __restrict__ counters, int n_counters) {
   // one thread per (plane row, plane); row index covers halo margins too (reflect of the padded signal)
   pdl_launch_dependents();
   pdl_wait();
+  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0)
+    for (int i = threadIdx.x; i < n_counters; i += blockDim.x) counters[i] = 0;
   const int L = T + 2 * pad;
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   const int pl = blockIdx.y, b = blockIdx.z;
@@ -811,12 +837,12 @@ __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int
   *reinterpret_cast<uint4*>(out + (((int64_t)b * planes + pl) * plane_rows + row) * 8) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
-__global__ void untile_kernel(const __nv_bfloat16* __restrict__ x, int C, int64_t L, int planes, int plane_rows,
+__global__ void untile_kernel(const __nv_bfloat16* __restrict__ x, int64_t batch_stride, int C, int64_t L, int plane_rows,
                               int halo, int undo_lrelu, float slope, float* __restrict__ out) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int c = blockIdx.y, b = blockIdx.z;
   if (t >= L) return;
-  float v = __bfloat162float(x[(((int64_t)b * planes + (c >> 3)) * plane_rows + halo + t) * 8 + (c & 7)]);
+  float v = __bfloat162float(x[(int64_t)b * batch_stride + ((int64_t)(c >> 3) * plane_rows + halo + t) * 8 + (c & 7)]);
   if (undo_lrelu && v < 0.f) v /= slope;
   out[((int64_t)b * C + c) * L + t] = v;
 }
@@ -898,6 +924,7 @@ TcLaunchCtx tc_launch_ctx(int device) {
   c.conv_persistent = env_int("TTSB200_CONV_PERSISTENT", 2);
   c.pqmf_direct = getenv("TTSB200_PQMF_DIRECT") ? 1 : 0;
   c.no_k24 = getenv("TTSB200_NO_K24") ? 1 : 0;
+  c.no_follow = getenv("TTSB200_NO_FOLLOW") ? 1 : 0;
   c.trace_file = getenv("TTSB200_STACK_TRACE");
   return c;
 }
@@ -932,6 +959,12 @@ ConvsPlan convs_plan(const TcConvParams& p) {
   return r;
 }
 }  // namespace
+
+int tc_conv_counts(const TcConvParams& p, int batch, const TcLaunchCtx& ctx) {
+  size_t smem = 0;
+  if (ctx.conv_persistent != 2 || convp_slots(p, &smem) <= 0 || p.ngroups > ctx.sms || batch <= 0) return 0;
+  return ceil_div(p.Lt, TC_TILE_M) * p.ngroups;   // (time tile, column group) units per utterance
+}
 
 cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCtx& ctx, cudaStream_t stream) {
   TcConvParams p = p_in;
@@ -985,16 +1018,16 @@ cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCt
 }
 
 cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out, int planes,
-                               int plane_rows, int halo, cudaStream_t stream) {
+                               int plane_rows, int halo, int* counters, int n_counters, cudaStream_t stream) {
   const dim3 grid(ceil_div(plane_rows, 128), planes, batch);
-  prep_mel_kernel<<<grid, 128, 0, stream>>>(mel, C, T, pad, out, planes, plane_rows, halo);
+  prep_mel_kernel<<<grid, 128, 0, stream>>>(mel, C, T, pad, out, planes, plane_rows, halo, counters, n_counters);
   return cudaGetLastError();
 }
 
-cudaError_t tc_untile_launch(const __nv_bfloat16* x, int batch, int C, int64_t L, int planes, int plane_rows, int halo,
-                             int undo_lrelu, float slope, float* out, cudaStream_t stream) {
+cudaError_t tc_untile_launch(const __nv_bfloat16* x, int64_t batch_stride, int batch, int C, int64_t L, int plane_rows,
+                             int halo, int undo_lrelu, float slope, float* out, cudaStream_t stream) {
   const dim3 grid(ceil_div(L, 256), C, batch);
-  untile_kernel<<<grid, 256, 0, stream>>>(x, C, L, planes, plane_rows, halo, undo_lrelu, slope, out);
+  untile_kernel<<<grid, 256, 0, stream>>>(x, batch_stride, C, L, plane_rows, halo, undo_lrelu, slope, out);
   return cudaGetLastError();
 }
 

@@ -249,6 +249,10 @@ inline CanonDims canon_dims(const ttsb200_plan* plan, int C, int64_t L) {
 
 struct Bf16Workspace {
   size_t mel_elems, buf_elems, head_floats, total_bytes;
+  size_t slab_elems;   // every activation tensor in the ping-pong buffers starts utterance b at b * slab_elems: a
+                       // kernel that follows its producer utterance by utterance (tc_common.cuh wait_counter) then
+                       // never touches a slab an older kernel still reads
+  int n_counters;   // per-utterance hand-over counters (one row of B per stage), zeroed by the first kernel of a forward
 };
 Bf16Workspace bf16_workspace(const ttsb200_plan* plan, int B, const Shape& sh) {
   const ttsb200_generator_config& cfg = plan->cfg;
@@ -257,9 +261,12 @@ Bf16Workspace bf16_workspace(const ttsb200_plan* plan, int B, const Shape& sh) {
   size_t mx = canon_dims(plan, cfg.base_channels, sh.L0).elems;
   for (size_t s = 0; s < plan->stages.size(); ++s)
     mx = std::max(mx, canon_dims(plan, plan->stages[s].Cout, sh.L[s]).elems);
-  w.buf_elems = (size_t)round_up((int64_t)B * mx, 128);
+  w.slab_elems = (size_t)round_up((int64_t)mx, 128);
+  w.buf_elems = (size_t)B * w.slab_elems;
   w.head_floats = (size_t)round_up((int64_t)B * cfg.out_channels * sh.L.back(), 64);
-  w.total_bytes = (w.mel_elems + 3 * w.buf_elems) * sizeof(__nv_bfloat16) + w.head_floats * sizeof(float);
+  w.n_counters = (int)round_up((int64_t)(2 * cfg.n_stages + 2) * B, 64);   // one row of B per counting launch
+  w.total_bytes = (w.mel_elems + 3 * w.buf_elems) * sizeof(__nv_bfloat16) + w.head_floats * sizeof(float) +
+                  (size_t)w.n_counters * sizeof(int);
   return w;
 }
 
@@ -278,6 +285,14 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   __nv_bfloat16* nxt = cur + wsz.buf_elems;
   __nv_bfloat16* hbuf = nxt + wsz.buf_elems;
   float* headf = reinterpret_cast<float*>(hbuf + wsz.buf_elems);
+  int* counters = reinterpret_cast<int*>(headf + wsz.head_floats);
+  // Hand-over between consecutive fused kernels utterance by utterance (tc_common.cuh wait_counter): the producer's
+  // counters and what they reach when an utterance is complete; null when the last kernel does not count.
+  const int* prod_done = nullptr;
+  int prod_target = 0;
+  const bool follow_ok = !plan->ctx.no_follow;
+  const int64_t slab = (int64_t)wsz.slab_elems;
+  int n_counting = 0;   // counting launches so far: each gets its own row of B counters
   cudaStream_t st = static_cast<cudaStream_t>(a->stream);
   Launcher ln{st, a->profile, B};
   const float* Wf = plan->blob;
@@ -300,7 +315,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   auto src = [&](const __nv_bfloat16* x, int C, int64_t L, int taps, int step, int first, bool lrelu) {
     const CanonDims d = canon_dims(plan, C, L);
     TcSrc s{};
-    s.x = x; s.batch_stride = (int64_t)d.elems; s.planes = d.planes; s.plane_rows = d.rows;
+    s.x = x; s.batch_stride = x == melc ? (int64_t)d.elems : slab; s.planes = d.planes; s.plane_rows = d.rows;
     const int lo = std::min(first, first + (taps - 1) * step);
     const int hi = std::max(first, first + (taps - 1) * step);
     s.row_base = halo + lo; s.rows = TC_TILE_M + (hi - lo); s.taps = taps;
@@ -310,7 +325,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   };
   auto canon_out = [&](TcConvParams& p, __nv_bfloat16* out, int C, int64_t L, bool lrelu, int margin) {
     const CanonDims d = canon_dims(plan, C, L);
-    p.out_mode = 0; p.out_c = out; p.out_batch_stride = (int64_t)d.elems; p.out_plane_rows = d.rows;
+    p.out_mode = 0; p.out_c = out; p.out_batch_stride = slab; p.out_plane_rows = d.rows;
     p.out_halo = halo; p.out_L = (int)L; p.out_lrelu = lrelu ? 1 : 0; p.margin = margin;
   };
   int trace_seq = 0;
@@ -318,14 +333,25 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     p.trace_id = layer * 10 + trace_seq++ % 10;   // label for the debug timeline (trace.cuh)
     if (tc_conv_smem_bytes(p) > 224 * 1024)
       return fail(TTSB200_ERR_INVALID, std::string(name) + ": tile does not fit shared memory on the BF16 path");
+    // the persistent kernel counts finished units per utterance and follows a counting producer
+    const int cnt = follow_ok ? tc_conv_counts(p, B, plan->ctx) : 0;
+    if (cnt > 0) {
+      if (prod_done) {
+        p.done_in = prod_done;
+        p.done_in_target = prod_target;
+      }
+      p.done_out = counters + (size_t)(n_counting++) * B;
+    }
     TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, plan->ctx, st); }));
+    prod_done = cnt > 0 ? p.done_out : nullptr;
+    prod_target = cnt;
     return 0;
   };
   auto tap = [&](int layer, const __nv_bfloat16* x, int C, int64_t L, bool undo, int x_halo) -> int {
     for (int i = 0; i < a->n_taps; ++i)
       if (a->tap_layers[i] == layer) {
         const CanonDims d = canon_dims(plan, C, L);
-        TTSB_CUDA(tc_untile_launch(x, B, C, L, d.planes, d.rows, x_halo, undo, slope, a->tap_out[i], st));
+        TTSB_CUDA(tc_untile_launch(x, slab, B, C, L, d.rows, x_halo, undo, slope, a->tap_out[i], st));
       }
     return 0;
   };
@@ -333,7 +359,8 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   {  // mel -> canonical bf16 (replicate inference padding + reflect margin folded in)
     const CanonDims d = canon_dims(plan, cfg.in_channels, sh.L0);
     TTSB_CUDA(ln.run("bf16.prep.mel", 0, 0.0, 4.0 * B * cfg.in_channels * a->frames + 2.0 * B * d.elems, [&] {
-      return tc_prep_mel_launch(a->mel, B, cfg.in_channels, a->frames, a->pad, melc, d.planes, d.rows, halo, st);
+      return tc_prep_mel_launch(a->mel, B, cfg.in_channels, a->frames, a->pad, melc, d.planes, d.rows, halo, counters,
+                                wsz.n_counters, st);
     }));
   }
   {
@@ -388,7 +415,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     TcStackParams q = stack_tiling(plan, s, fuse_head, fuse_up);
     if (q.kt > 0) {  // whole ResidualStack in one kernel
       const CanonDims din = canon_dims(plan, C, L);
-      q.x = cur; q.x_batch_stride = (int64_t)din.elems; q.x_plane_rows = din.rows; q.x_halo = cur_halo;
+      q.x = cur; q.x_batch_stride = slab; q.x_plane_rows = din.rows; q.x_halo = cur_halo;
       cur_halo = halo;
       q.L = (int)L; q.slope = slope;
       for (int bi = 0; bi < nb; ++bi) {
@@ -398,7 +425,17 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         q.b1[bi] = Wf + bp.tc_conv1.groups[0].bias_off;
         q.b2s[bi] = Wf + bp.tc_conv2s.groups[0].bias_off;
       }
-      q.out = TcCanonOut{nxt, (int64_t)din.elems, din.rows, halo, (int)L, 1, last_stage ? 1 : 2};
+      q.out = TcCanonOut{nxt, slab, din.rows, halo, (int)L, 1, last_stage ? 1 : 2};
+      // Follow the previous kernel utterance by utterance when it counted its work.  Several kernels of the chain may
+      // then be in flight; this one writes `nxt`, which an older kernel may still be reading — but only slabs of
+      // utterances this kernel has not reached: it starts utterance b after its producer has finished b, which has
+      // itself waited for ITS producer to finish b, and so on down the chain.
+      const bool follow = follow_ok && prod_done != nullptr;
+      if (follow) {
+        q.done_in = prod_done;
+        q.done_in_target = prod_target;
+      }
+      q.done_out = follow_ok ? counters + (size_t)(n_counting++) * B : nullptr;
       double macs = (double)(cfg.res_kernel + 2) * nb * C * C * L * B;
       double bytes = 2.0 * (2.0 * B * C * L + (double)(cfg.res_kernel + 2) * nb * C * C);
       if (fuse_head) {
@@ -413,13 +450,15 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         const CanonDims dn = canon_dims(plan, nx.Cout, sh.L[s + 1]);
         // rows q f - P .. of one GEMM row go out as 32-byte stores: keep (halo - P) even
         cur_halo = halo + ((halo - nx.P) & 1);
-        q.up_out = TcCanonOut{nxt, (int64_t)dn.elems, dn.rows, cur_halo, (int)sh.L[s + 1], 0, 0};
+        q.up_out = TcCanonOut{nxt, slab, dn.rows, cur_halo, (int)sh.L[s + 1], 0, 0};
         macs += 2.0 * nx.f * C * nx.Cout * L * B;
         bytes = 2.0 * B * (C * L + (double)nx.Cout * sh.L[s + 1]);
         up_done = true;
       }
       TTSB_CUDA(ln.run(fuse_head ? "bf16.resstack.fused+head" : fuse_up ? "bf16.resstack.fused+convT" : "bf16.resstack.fused",
                        sp.layer_stack, 2 * macs, bytes, [&] { return tc_stack_launch(q, B, plan->ctx, st); }));
+      prod_done = q.done_out;
+      prod_target = q.done_out ? tc_stack_signals_per_utterance(q) : 0;
       std::swap(cur, nxt);
     } else
     for (int bi = 0; bi < nb; ++bi) {
@@ -465,7 +504,8 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         return rc;
     }
     if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
-    if (int rc = finish_output(plan, a, ln, dst, to_out, Lin)) return rc;
+    // the PQMF kernel follows a counting head kernel utterance by utterance
+    if (int rc = finish_output(plan, a, ln, dst, to_out, Lin, head_done ? prod_done : nullptr, prod_target)) return rc;
   }
   return 0;
 }

@@ -57,7 +57,9 @@ constexpr int RING_KB = 64;
 constexpr int RING_MAX_SLOTS = 12;
 // Service warps after the epilogue groups: bulk-copy producer (+ TMEM owner), dilated-conv MMA issuer, and a third
 // warp that is the pointwise (1x1 pair + fused tail) MMA issuer, or in ring mode the second weight producer.
-constexpr int SERVICE_THREADS = 96;
+// A fourth one counts finished items for the next kernel (done_out): the fence that publishes an item's stores
+// stalls whoever executes it until they have drained, so it must not be an epilogue warp (measured: +7..10 % per kernel).
+constexpr int SERVICE_THREADS = 128;
 
 
 #ifdef TTSB_STACK_TRACE
@@ -72,6 +74,7 @@ struct Bars {
   uint64_t xa_ready[MAX_KT], xr_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
   uint64_t ring_full[RING_MAX_SLOTS], ring_empty[RING_MAX_SLOTS];
   uint64_t edge[4 * MAX_KT];   // fused head: warp w's first / last three accumulator rows are in the edge buffer
+  uint64_t item_done;          // every epilogue warp has issued its stores of the item (-> the signal warp)
 };
 
 // TAIL: what follows the last block — 0 the stack output is stored, 1 fused output head, 2 fused transposed conv
@@ -173,6 +176,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       mbar_init(&bars.ring_empty[i], 1);
     }
     for (int i = 0; i < 4 * MAX_KT; ++i) mbar_init(&bars.edge[i], 32);
+    mbar_init(&bars.item_done, KT * CS * 4);
     for (int t = 0; t < KT; ++t) {
       mbar_init(&bars.xa_ready[t], GROUP_THREADS);
       mbar_init(&bars.xr_ready[t], GROUP_THREADS);
@@ -184,6 +188,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   }
   constexpr int PRODUCER_WARP = KT * CS * 4, MMA_WARP = PRODUCER_WARP + 1;
   constexpr int THIRD_WARP = MMA_WARP + 1;       // ring mode: issues the odd weight chunks; else: pointwise MMA issuer
+  constexpr int SIGNAL_WARP = THIRD_WARP + 1;    // publishes finished items to the next kernel
   if (warp == PRODUCER_WARP) tmem_alloc(&tmem_base_s, TMEM_ALLOC);
   if (!BIAS_MMA) {
     for (int e = tid; e < nb * 2 * CP; e += NT) {
@@ -213,17 +218,26 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
   pdl_launch_dependents();
-  if (warp != PRODUCER_WARP) pdl_wait();   // the producer first prefetches weights (not written by any kernel)
+  // With done_in the previous kernel is followed utterance by utterance (the loader polls its counters) and nobody
+  // waits for its whole grid; what this kernel writes is then never a buffer the previous kernel still reads.
+  const bool follow = p.done_in != nullptr;
+  if (warp != PRODUCER_WARP && !follow) pdl_wait();   // the producer first prefetches weights (not written by any kernel)
 
   if (warp == PRODUCER_WARP) {
     // =============================== producer ===============================
     if (elect_one()) {
+      int ready_b = -1;   // utterances up to here are complete in the previous kernel (follow mode)
       auto load_x = [&](int it) {
         const int item = blockIdx.x + it * gridDim.x;
         if (item >= n_items) return;
         const int buf = it & 1;
         if (it >= 2) mbar_wait(&bars.x_free[buf], ((it >> 1) - 1) & 1);
         const int b = item / p.n_chains, chain = item - b * p.n_chains;
+        if (follow && b > ready_b) {
+          wait_counter(p.done_in + b, p.done_in_target);
+          fence_proxy_async_global();
+          ready_b = b;
+        }
         const int g0 = chain * V - SD;
         mbar_expect_tx(&bars.x_full[buf], (uint32_t)PL * TR * 16);
         const __nv_bfloat16* gx = p.x + (int64_t)b * p.x_batch_stride + (int64_t)(p.x_halo + g0) * 8;
@@ -239,7 +253,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         mbar_expect_tx(&bars.wh_full, up_bytes);
         bulk_g2s(sWH, p.up_w, up_bytes, &bars.wh_full);
       }
-      pdl_wait();   // the previous kernel's output is complete from here on
+      if (!follow) pdl_wait();   // the previous kernel's output is complete from here on
       load_x(0);
       const bool up_stream = up && p.up_mode == 2;   // tail weights take turns with W2S in its slot
       auto load_up = [&](uint32_t& n_w2) {
@@ -598,6 +612,19 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           umma_commit(&bars.x_free[buf]);
         }
         __syncwarp();
+      }
+    }
+  } else if (warp == SIGNAL_WARP) {
+    // =============================== signal warp ===============================
+    // Item by item: once every epilogue warp has issued its stores (item_done: their arrive releases them to this
+    // thread), make them visible device-wide and count the item for its utterance.  The next kernel's loader polls
+    // that counter (wait_counter) instead of waiting for this whole grid.
+    if (p.done_out && elect_one()) {
+      for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
+        const int b = (blockIdx.x + it * gridDim.x) / p.n_chains;
+        mbar_wait(&bars.item_done, it & 1);
+        __threadfence();
+        atomicAdd(p.done_out + b, 1);
       }
     }
   } else {
@@ -1059,6 +1086,12 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         else head_epi(std::integral_constant<int, 1>{});
         tr(245);
       }
+      auto signal_item = [&]() {   // this warp's stores of the item are out: count it for utterance b
+        if (p.done_out) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars.item_done);
+        }
+      };
       if (up) {
         // ---- epilogue 3: transposed-conv accumulator -> next stage's input; GEMM row q holds output rows
         // q f - P .. q f - P + f - 1, columns ordered [plane][phase][8]
@@ -1107,6 +1140,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         }
         tr(231);
       }
+      signal_item();
     }
   }
   tc_fence_before();
@@ -1243,6 +1277,11 @@ size_t tc_stack_smem_bytes(const TcStackParams& p) {
          (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
          head_smem_bytes(p) +
          (p.up_w && p.up_mode == 1 ? (size_t)2 * p.cp * p.up_n * 2 : 0);
+}
+
+int tc_stack_signals_per_utterance(const TcStackParams& p) {
+  const int V = p.kt * 128 - 2 * (p.sum_d + (p.head_w ? (p.head_taps - 1) / 2 : p.up_w ? 1 : 0));
+  return ceil_div(p.L + (p.up_w ? 1 : 0), V);   // one count per finished chain
 }
 
 cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, const TcLaunchCtx& ctx, cudaStream_t stream) {

@@ -18,6 +18,7 @@ struct TcLaunchCtx {
   int conv_persistent = 2;     // TTSB200_CONV_PERSISTENT: 2 weights-resident persistent kernel (narrow column groups,
                                // the default: fastest at cfg2), 1 activation-resident persistent kernel (weights
                                // streamed, N = 192-256 per MMA; measured 0.321 vs 0.309 ms per step), 0 generic only
+  int no_follow = 0;           // TTSB200_NO_FOLLOW: every kernel waits for the whole previous grid (A/B experiments)
   int no_k24 = 0;              // TTSB200_NO_K24: keep the six-K-step dilated conv on 24-channel stages (A/B experiments)
   int pqmf_direct = 0;         // TTSB200_PQMF_DIRECT: direct 63-tap synthesis instead of the factorised form
   const char* trace_file = nullptr;   // TTSB200_STACK_TRACE (trace builds only)
@@ -72,6 +73,12 @@ struct TcConvParams {
   float* out_f;           // fp32 NCL out [B][cout_real][out_L]
   int cout_real;
   float slope;
+  // Hand-over per utterance (tc_common.cuh wait_counter; persistent kernel only — tc_conv_counts()): done_out[b] += 1
+  // per finished (time tile, column group) of utterance b; with done_in the loaders poll the previous kernel's
+  // counters instead of the kernel waiting for that whole grid.
+  int* done_out;
+  const int* done_in;
+  int done_in_target;
   long long* trace;       // optional timeline buffer (trace.cuh)
   int trace_id;
   int debug;              // knock-out bits for timeline experiments (trace builds only)
@@ -131,6 +138,12 @@ struct TcStackParams {
   int up_f, up_P, up_n;          // stride, output offset (padding), GEMM columns = f * C_next_pad
   int up_mode;                   // filled by tc_stack_configure: 1 weights resident, 2 streamed through the W2S slot
   TcCanonOut up_out;             // raw input of the next stage's stack (no margins), L = next length
+  // Hand-over between consecutive kernels per utterance instead of per grid (tc_common.cuh wait_counter):
+  // done_out[b] += 1 per finished item (chain) of utterance b; with done_in the kernel skips
+  // griddepcontrol.wait and its loader waits for done_in[b] >= done_in_target before the first load of utterance b.
+  int* done_out;
+  const int* done_in;
+  int done_in_target;
   int debug;               // knock-out bits for timeline experiments (trace builds only)
   long long* trace;        // optional (TTSB200_STACK_TRACE): [role][256] {tag, clock} pairs written by CTA 0
   TcCanonOut out;
@@ -142,15 +155,22 @@ int tc_stack_cs(int cp);                          // epilogue warps per TMEM lan
 bool tc_stack_configure(TcStackParams& p);        // fills kt / sum_d / guard / w_sets from cp, dil[], nblocks
 size_t tc_stack_smem_bytes(const TcStackParams& p);
 cudaError_t tc_stack_launch(const TcStackParams& p, int batch, const TcLaunchCtx& ctx, cudaStream_t stream);
+int tc_stack_signals_per_utterance(const TcStackParams& p);   // what done_out[b] reaches when utterance b is complete
 
 size_t tc_conv_smem_bytes(const TcConvParams& p);
+// True when tc_conv_launch will run this launch on the persistent weights-resident kernel, the one that counts
+// finished work per utterance (done_out) and can follow a counting producer (done_in); 0 otherwise.  The value is what
+// done_out[b] reaches when utterance b is complete.
+int tc_conv_counts(const TcConvParams& p, int batch, const TcLaunchCtx& ctx);
 cudaError_t tc_conv_launch(const TcConvParams& p, int batch, const TcLaunchCtx& ctx, cudaStream_t stream);
 
 // mel fp32 [B][C][T] -> canonical bf16 with replicate padding `pad` folded in and reflect margins
+// ... and zeroes `n_counters` hand-over counters (first kernel of a forward, ordered behind everything before it)
 cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out,
-                               int planes, int plane_rows, int halo, cudaStream_t stream);
+                               int planes, int plane_rows, int halo, int* counters, int n_counters,
+                               cudaStream_t stream);
 // canonical bf16 -> fp32 NCL (per-layer parity taps); undo_lrelu inverts a stored activation
-cudaError_t tc_untile_launch(const __nv_bfloat16* x, int batch, int C, int64_t L, int planes, int plane_rows,
+cudaError_t tc_untile_launch(const __nv_bfloat16* x, int64_t batch_stride, int batch, int C, int64_t L, int plane_rows,
                              int halo, int undo_lrelu, float slope, float* out, cudaStream_t stream);
 
 }  // namespace ttsb
