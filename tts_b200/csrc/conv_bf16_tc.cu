@@ -1020,8 +1020,11 @@ cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCt
 cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out, int planes,
                                int plane_rows, int halo, int* counters, int n_counters, cudaStream_t stream) {
   const dim3 grid(ceil_div(plane_rows, 128), planes, batch);
-  prep_mel_kernel<<<grid, 128, 0, stream>>>(mel, C, T, pad, out, planes, plane_rows, halo, counters, n_counters);
-  return cudaGetLastError();
+  // Launched behind the previous kernel of the stream like every other kernel of the chain: its CTAs are resident
+  // when that kernel (the last one of the previous inference) drains, and griddepcontrol.wait inside holds them
+  // until it has completed — which is also when its counters may be zeroed.
+  return launch_pdl(prep_mel_kernel, grid, dim3(128), 0, stream, mel, C, T, pad, out, planes, plane_rows, halo, counters,
+                    n_counters);
 }
 
 cudaError_t tc_untile_launch(const __nv_bfloat16* x, int64_t batch_stride, int batch, int C, int64_t L, int plane_rows,
