@@ -215,7 +215,8 @@ class LongformPlan:
         raise RuntimeError("LongformPlan: no destination mapping available: " + "; ".join(errors))
 
     def describe(self):
-        return {"mode": self.mode, "why": self.why, "dst_rank": self.dst_rank, "halo_frames": self.halo,
+        return {"mode": self.mode, "why": self.why, "launch": getattr(self, "graph_note", "eager"),
+                "dst_rank": self.dst_rank, "halo_frames": self.halo,
                 "frames_per_rank": [e - s for s, e in self.parts],
                 "recomputed_halo_frames_per_rank": [min(self.frames, e + self.halo) - max(0, s - self.halo) - (e - s)
                                                     for s, e in self.parts]}
@@ -250,5 +251,40 @@ class LongformPlan:
         self._barrier()
         return self.local if self.rank == self.dst_rank else None
 
+    def graphed(self, mel):
+        """``run(mel)`` captured once into a CUDA graph; returns ``replay() -> waveform (dst_rank) / None``.
+
+        At N ranks a rank's kernels take ~1/N of the one-GPU time while the host side of ``run`` — the window slice,
+        a dozen launches through the C ABI, the barrier — stays what it was: with many ranks the host, not the GPUs,
+        would set the pace.  The shapes are fixed by the plan, so everything is captured for THIS ``mel`` tensor
+        (callers refill it in place) and replayed with one launch.  Collective: every rank of the group calls it.
+        Falls back to the eager ``run`` (and says why in ``describe()``) where the barrier cannot be captured."""
+        if self.mode == "gather" or self.device.type != "cuda":
+            return lambda: self.run(mel)
+        dev = self.device
+        cur = torch.cuda.current_stream(dev)
+        try:
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):      # warm-up off the capture: plan, workspace, attribute calls
+                self.run(mel)
+            cur.wait_stream(side)
+            torch.cuda.synchronize(dev)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self.run(mel)
+        except Exception as exc:               # e.g. a barrier implementation that refuses stream capture
+            self.graph_note = f"eager ({type(exc).__name__}: {str(exc)[:120]})"
+            torch.cuda.synchronize(dev)
+            return lambda: self.run(mel)
+        self.graph_note = "cuda graph"
+        self._graph = graph
+
+        def replay():
+            graph.replay()
+            return self.local if self.rank == self.dst_rank else None
+        return replay
+
     def close(self):
+        self._graph = None
         self.dest = self.local = self._hdl = self._ipc_keep = None
