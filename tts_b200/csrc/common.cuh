@@ -107,10 +107,11 @@ cudaError_t f32_to_f16_launch(const float* x, void* y, int64_t n, cudaStream_t s
 constexpr int PQMF_FACT_TABLE = 96;
 bool pqmf_factor_4x63(const float* G_host, float* tbl_host);
 bool pqmf_fact_usable(const float* x, int64_t Ts);
-// done_in (optional): per-utterance counters of the kernel that writes x; the launch then follows that kernel
-// utterance by utterance instead of waiting for its whole grid (tc_common.cuh wait_counter).
+// follow (optional): how the kernel that writes x counts its finished work; the launch then follows that kernel
+// segment by segment instead of waiting for its whole grid (follow.cuh).
+struct TcFollow;
 cudaError_t pqmf_synthesis_fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, void* y, int out_f16,
-                                       const PqmfCrop* crop, const int* done_in, int done_target, cudaStream_t stream);
+                                       const PqmfCrop* crop, const TcFollow* follow, cudaStream_t stream);
 cudaError_t pqmf_analysis_launch(const float* x, const float* H, int batch, int bands, int taps,
                                  int64_t T, float* y, cudaStream_t stream);
 

@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
   __shared__ __align__(16) float s_bias[256];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bool follow = p.done_in != nullptr;   // the previous kernel is followed utterance by utterance
+  const bool follow = p.follow.done != nullptr;   // the previous kernel is followed segment by segment (follow.cuh)
   const int ngroups = p.ngroups;
   const TcGroup& G = p.grp[blockIdx.x % ngroups];
   const int ncols = G.ncols;
@@ -483,9 +483,10 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
     if (p.done_out && elect_one()) {
       int i = 0;
       for (int u = first; u < n_units; u += stride, ++i) {
+        const int b = u / n_tiles, tile = u - b * n_tiles;
         mbar_wait(&unit_done, i & 1);
         __threadfence();
-        atomicAdd(p.done_out + u / n_tiles, 1);
+        atomicAdd(p.done_out + b * FOLLOW_SEGS + tile / p.count_units_per_seg, 1);
       }
     }
   } else if (warp == 0 || warp == PRODUCER2) {
@@ -498,14 +499,10 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
         if (!follow) pdl_wait();
       }
       uint32_t gc = 0;
-      int ready_b = -1;
+      FollowState fst;
       for (int u = first; u < n_units; u += stride) {
         const int b = u / n_tiles, t0 = (u - b * n_tiles) * TC_TILE_M;
-        if (follow && b > ready_b) {
-          wait_counter(p.done_in + b, p.done_in_target);
-          fence_proxy_async_global();
-          ready_b = b;
-        }
+        if (follow) follow_wait(p.follow, b, t0 + p.follow_in_lo, t0 + p.follow_in_lo + S.rows, fst);
         const __nv_bfloat16* gx = S.x + (int64_t)b * S.batch_stride + (int64_t)(S.row_base + t0) * 8;
         for (int c = 0; c < nchunks; ++c, ++gc) {
           if ((gc & 1) != mine) continue;
@@ -960,10 +957,15 @@ ConvsPlan convs_plan(const TcConvParams& p) {
 }
 }  // namespace
 
-int tc_conv_counts(const TcConvParams& p, int batch, const TcLaunchCtx& ctx) {
+bool tc_conv_count_info(const TcConvParams& p, int batch, const TcLaunchCtx& ctx, int* n_units, int* unit_rows,
+                        int* row_offset, int* mult) {
   size_t smem = 0;
-  if (ctx.conv_persistent != 2 || convp_slots(p, &smem) <= 0 || p.ngroups > ctx.sms || batch <= 0) return 0;
-  return ceil_div(p.Lt, TC_TILE_M) * p.ngroups;   // (time tile, column group) units per utterance
+  if (ctx.conv_persistent != 2 || convp_slots(p, &smem) <= 0 || p.ngroups > ctx.sms || batch <= 0) return false;
+  *n_units = ceil_div(p.Lt, TC_TILE_M);   // time tiles per utterance, each finished once per column group
+  *unit_rows = TC_TILE_M * p.up_f;        // GEMM row q -> output rows q f - P .. q f - P + f - 1
+  *row_offset = p.up_P;
+  *mult = p.ngroups;
+  return true;
 }
 
 cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCtx& ctx, cudaStream_t stream) {

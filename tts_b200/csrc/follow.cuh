@@ -1,0 +1,64 @@
+// Kernel hand-over per time segment instead of per grid.
+//
+// A producer kernel (persistent conv kernel, fused stack kernel) counts finished work units in global memory, one
+// counter per (utterance, segment of `units_per_seg` consecutive units along time): every epilogue warp arrives on a
+// shared-memory mbarrier after its last store of the unit, a dedicated signal warp waits for that barrier and executes
+// __threadfence + atomicAdd.  A consumer launched behind it with programmatic dependent launch never executes
+// griddepcontrol.wait: its loader thread polls, with acquire loads, the counters of the segments that cover the rows
+// it is about to read, then fence.proxy.async.global (its bulk copies read through the async proxy).  Work units are
+// ordered (utterance, time) in every kernel, so a consumer CTA that lands on an SM the producer's tail has left idle
+// starts at the beginning of the data while the producer is still finishing its end.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ttsb {
+
+constexpr int FOLLOW_SEGS = 32;   // counters per utterance and counting launch
+
+struct TcFollow {
+  const int* done;        // producer's counters [batch][FOLLOW_SEGS]; nullptr = wait for the whole previous grid
+  int unit_rows;          // rows of the producer's output one of its work units covers ...
+  int row_offset;         // ... row r belongs to unit (r + row_offset) / unit_rows
+  int units_per_seg;
+  int n_units;            // per utterance
+  int mult;               // counts per finished unit (column groups of the persistent conv kernel)
+};
+
+#ifdef __CUDACC__
+struct FollowState {
+  int b = -1, seg = -1;   // segments up to `seg` of utterance `b` are known complete
+};
+
+// Blocks until the producer has finished every unit that covers rows [a0, a1) of utterance b (rows outside the
+// tensor belong to its first / last unit, whose epilogues write the margins).  One thread.
+__device__ __forceinline__ void follow_wait(const TcFollow& f, int b, int a0, int a1, FollowState& st) {
+  a0 = a0 < 0 ? 0 : a0;
+  a1 = a1 < 1 ? 1 : a1;
+  int u0 = (a0 + f.row_offset) / f.unit_rows, u1 = (a1 - 1 + f.row_offset) / f.unit_rows;
+  u0 = u0 < f.n_units ? u0 : f.n_units - 1;
+  u1 = u1 < f.n_units ? u1 : f.n_units - 1;
+  const int s0 = u0 / f.units_per_seg, s1 = u1 / f.units_per_seg;
+  if (st.b != b) {
+    st.b = b;
+    st.seg = -1;
+  }
+  if (s1 <= st.seg) return;
+  for (int s = s0 > st.seg + 1 ? s0 : st.seg + 1; s <= s1; ++s) {
+    const int left = f.n_units - s * f.units_per_seg;
+    const int target = (left < f.units_per_seg ? left : f.units_per_seg) * f.mult;
+    const int* p = f.done + b * FOLLOW_SEGS + s;
+    for (;;) {
+      int v;
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+      if (v >= target) break;
+      __nanosleep(64);
+    }
+  }
+  st.seg = s1;
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+#endif
+
+}  // namespace ttsb

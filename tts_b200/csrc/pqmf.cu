@@ -18,6 +18,7 @@
 #include <cuda_fp16.h>
 
 #include "common.cuh"
+#include "follow.cuh"
 
 namespace ttsb {
 
@@ -187,7 +188,7 @@ template <typename OutT>
 __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const float* x,
                                                                            const float* __restrict__ tbl,
                                                                            OutT* __restrict__ y, int Ts, PqmfOut o,
-                                                                           const int* done_in, int done_target) {
+                                                                           const TcFollow follow) {
   __shared__ __align__(16) float sv[8][SF_WIN];
   __shared__ __align__(16) float st[PQMF_FACT_TABLE];   // [p][k] modulation, then [p][8] FIR taps
 
@@ -198,16 +199,12 @@ __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const 
 
   pdl_launch_dependents();
   if (tid < PQMF_FACT_TABLE) st[tid] = tbl[tid];
-  // The head kernel counts finished items per utterance (tc_common.cuh wait_counter): follow it utterance by
-  // utterance when it does, else wait for its whole grid.
-  if (done_in) {
+  // The head kernel counts finished chains per time segment (follow.cuh): follow it segment by segment when it
+  // does, else wait for its whole grid.
+  if (follow.done) {
     if (tid == 0) {
-      while (true) {
-        int v;
-        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(done_in + b) : "memory");
-        if (v >= done_target) break;
-        __nanosleep(64);
-      }
+      FollowState fst;
+      follow_wait(follow, b, q0 - 8, q0 + SF_TILE + 8, fst);
     }
   } else {
     pdl_wait();   // the head's sub-band signals are complete from here on
@@ -366,15 +363,14 @@ bool pqmf_factor_4x63(const float* G, float* tbl) {
 
 namespace {
 template <typename OutT>
-cudaError_t fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, OutT* y, PqmfOut o, const int* done_in,
-                        int done_target, cudaStream_t stream) {
+cudaError_t fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, OutT* y, PqmfOut o, const TcFollow& follow,
+                        cudaStream_t stream) {
   // shared-memory carve-out preference: a hint, set once per process (first device that launches)
   static const cudaError_t carve = cudaFuncSetAttribute(pqmf_synth_4x63_fact_kernel<OutT>,
                                                         cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   if (carve != cudaSuccess) return carve;
   const dim3 grid(ceil_div(Ts, SF_TILE), batch);
-  return launch_pdl(pqmf_synth_4x63_fact_kernel<OutT>, grid, dim3(SF_THREADS), 0, stream, x, tbl, y, (int)Ts, o, done_in,
-                    done_target);
+  return launch_pdl(pqmf_synth_4x63_fact_kernel<OutT>, grid, dim3(SF_THREADS), 0, stream, x, tbl, y, (int)Ts, o, follow);
 }
 template <typename OutT>
 cudaError_t direct_launch(const float* x, const float* G, int batch, int bands, int taps, int64_t Ts, OutT* y,
@@ -404,11 +400,12 @@ PqmfOut make_out(const PqmfCrop* crop, int64_t Tout) {
 }  // namespace
 
 cudaError_t pqmf_synthesis_fact_launch(const float* x, const float* tbl, int batch, int64_t Ts, void* y, int out_f16,
-                                       const PqmfCrop* crop, const int* done_in, int done_target, cudaStream_t stream) {
+                                       const PqmfCrop* crop, const TcFollow* follow, cudaStream_t stream) {
   if (batch <= 0 || Ts <= 0) return cudaSuccess;
   const PqmfOut o = make_out(crop, 4 * Ts);
-  return out_f16 ? fact_launch(x, tbl, batch, Ts, static_cast<__half*>(y), o, done_in, done_target, stream)
-                 : fact_launch(x, tbl, batch, Ts, static_cast<float*>(y), o, done_in, done_target, stream);
+  const TcFollow f = follow ? *follow : TcFollow{};
+  return out_f16 ? fact_launch(x, tbl, batch, Ts, static_cast<__half*>(y), o, f, stream)
+                 : fact_launch(x, tbl, batch, Ts, static_cast<float*>(y), o, f, stream);
 }
 // usable when whole float4s of every band are in or out of range and aligned
 bool pqmf_fact_usable(const float* x, int64_t Ts) {

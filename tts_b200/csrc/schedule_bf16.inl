@@ -247,25 +247,36 @@ inline CanonDims canon_dims(const ttsb200_plan* plan, int C, int64_t L) {
   return d;
 }
 
+// Elements between consecutive utterances of a canonical [C, L] tensor.
+inline size_t act_stride(const ttsb200_plan* plan, int C, int64_t L) {
+  return (size_t)round_up((int64_t)canon_dims(plan, C, L).elems, 128);
+}
+
+// Workspace: the canonical mel, then ONE region per activation tensor of the schedule (no ping-pong: with the
+// hand-over per time segment, follow.cuh, several kernels of the chain are in flight on the same utterance, so a
+// kernel must never write where an older one may still read), a scratch tensor for the per-conv fallback, the fp32
+// head output and the hand-over counters.  The tensors grow 2x to 8x per stage, so their sum is ~1.3 x the largest
+// one times the three ping-pong buffers there used to be.
 struct Bf16Workspace {
-  size_t mel_elems, buf_elems, head_floats, total_bytes;
-  size_t slab_elems;   // every activation tensor in the ping-pong buffers starts utterance b at b * slab_elems: a
-                       // kernel that follows its producer utterance by utterance (tc_common.cuh wait_counter) then
-                       // never touches a slab an older kernel still reads
-  int n_counters;   // per-utterance hand-over counters (one row of B per stage), zeroed by the first kernel of a forward
+  size_t mel_elems, act_elems, head_floats, total_bytes;
+  int n_counters;   // [counting launch][B][FOLLOW_SEGS], zeroed by the first kernel of a forward
 };
 Bf16Workspace bf16_workspace(const ttsb200_plan* plan, int B, const Shape& sh) {
   const ttsb200_generator_config& cfg = plan->cfg;
   Bf16Workspace w{};
   w.mel_elems = (size_t)round_up((int64_t)B * canon_dims(plan, cfg.in_channels, sh.L0).elems, 128);
-  size_t mx = canon_dims(plan, cfg.base_channels, sh.L0).elems;
-  for (size_t s = 0; s < plan->stages.size(); ++s)
-    mx = std::max(mx, canon_dims(plan, plan->stages[s].Cout, sh.L[s]).elems);
-  w.slab_elems = (size_t)round_up((int64_t)mx, 128);
-  w.buf_elems = (size_t)B * w.slab_elems;
+  // projection output; per stage the transposed conv's output and the stack's (or, per-conv fallback, the second
+  // ping-pong tensor); one scratch tensor (h of the per-conv fallback) as large as the largest
+  size_t sum = act_stride(plan, cfg.base_channels, sh.L0), mx = sum;
+  for (size_t s = 0; s < plan->stages.size(); ++s) {
+    const size_t e = act_stride(plan, plan->stages[s].Cout, sh.L[s]);
+    sum += 2 * e;
+    mx = std::max(mx, e);
+  }
+  w.act_elems = (size_t)B * (sum + mx);
   w.head_floats = (size_t)round_up((int64_t)B * cfg.out_channels * sh.L.back(), 64);
-  w.n_counters = (int)round_up((int64_t)(2 * cfg.n_stages + 2) * B, 64);   // one row of B per counting launch
-  w.total_bytes = (w.mel_elems + 3 * w.buf_elems) * sizeof(__nv_bfloat16) + w.head_floats * sizeof(float) +
+  w.n_counters = (int)round_up((int64_t)(2 * cfg.n_stages + 2) * B * FOLLOW_SEGS, 64);
+  w.total_bytes = (w.mel_elems + w.act_elems) * sizeof(__nv_bfloat16) + w.head_floats * sizeof(float) +
                   (size_t)w.n_counters * sizeof(int);
   return w;
 }
@@ -281,18 +292,26 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   if (!a->workspace || a->workspace_bytes < wsz.total_bytes)
     return fail(TTSB200_ERR_WORKSPACE, "workspace smaller than ttsb200_workspace_bytes()");
   __nv_bfloat16* melc = static_cast<__nv_bfloat16*>(a->workspace);
-  __nv_bfloat16* cur = melc + wsz.mel_elems;
-  __nv_bfloat16* nxt = cur + wsz.buf_elems;
-  __nv_bfloat16* hbuf = nxt + wsz.buf_elems;
-  float* headf = reinterpret_cast<float*>(hbuf + wsz.buf_elems);
+  __nv_bfloat16* act = melc + wsz.mel_elems;     // bump-allocated: one region per activation tensor
+  size_t act_used = 0;
+  auto fresh = [&](int C, int64_t L) {
+    __nv_bfloat16* p = act + act_used;
+    act_used += (size_t)B * act_stride(plan, C, L);
+    return p;
+  };
+  __nv_bfloat16* cur = nullptr;                  // the tensor the next launch reads
+  float* headf = reinterpret_cast<float*>(act + wsz.act_elems);
   int* counters = reinterpret_cast<int*>(headf + wsz.head_floats);
   // Hand-over between consecutive fused kernels utterance by utterance (tc_common.cuh wait_counter): the producer's
   // counters and what they reach when an utterance is complete; null when the last kernel does not count.
-  const int* prod_done = nullptr;
-  int prod_target = 0;
+  TcFollow prod{};   // how the last launch counts its finished work; done == nullptr: it does not
   const bool follow_ok = !plan->ctx.no_follow;
-  const int64_t slab = (int64_t)wsz.slab_elems;
-  int n_counting = 0;   // counting launches so far: each gets its own row of B counters
+  int n_counting = 0;   // counting launches so far: each gets its own [B][FOLLOW_SEGS] block of counters
+  auto counting = [&](int n_units, int unit_rows, int row_offset, int mult, int** done_out, int* units_per_seg) {
+    *done_out = counters + (size_t)(n_counting++) * B * FOLLOW_SEGS;
+    *units_per_seg = ceil_div(n_units, FOLLOW_SEGS);
+    return TcFollow{*done_out, unit_rows, row_offset, *units_per_seg, n_units, mult};
+  };
   cudaStream_t st = static_cast<cudaStream_t>(a->stream);
   Launcher ln{st, a->profile, B};
   const float* Wf = plan->blob;
@@ -315,7 +334,8 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   auto src = [&](const __nv_bfloat16* x, int C, int64_t L, int taps, int step, int first, bool lrelu) {
     const CanonDims d = canon_dims(plan, C, L);
     TcSrc s{};
-    s.x = x; s.batch_stride = x == melc ? (int64_t)d.elems : slab; s.planes = d.planes; s.plane_rows = d.rows;
+    s.x = x; s.batch_stride = x == melc ? (int64_t)d.elems : (int64_t)act_stride(plan, C, L);
+    s.planes = d.planes; s.plane_rows = d.rows;
     const int lo = std::min(first, first + (taps - 1) * step);
     const int hi = std::max(first, first + (taps - 1) * step);
     s.row_base = halo + lo; s.rows = TC_TILE_M + (hi - lo); s.taps = taps;
@@ -325,7 +345,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   };
   auto canon_out = [&](TcConvParams& p, __nv_bfloat16* out, int C, int64_t L, bool lrelu, int margin) {
     const CanonDims d = canon_dims(plan, C, L);
-    p.out_mode = 0; p.out_c = out; p.out_batch_stride = slab; p.out_plane_rows = d.rows;
+    p.out_mode = 0; p.out_c = out; p.out_batch_stride = (int64_t)act_stride(plan, C, L); p.out_plane_rows = d.rows;
     p.out_halo = halo; p.out_L = (int)L; p.out_lrelu = lrelu ? 1 : 0; p.margin = margin;
   };
   int trace_seq = 0;
@@ -334,24 +354,23 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     if (tc_conv_smem_bytes(p) > 224 * 1024)
       return fail(TTSB200_ERR_INVALID, std::string(name) + ": tile does not fit shared memory on the BF16 path");
     // the persistent kernel counts finished units per utterance and follows a counting producer
-    const int cnt = follow_ok ? tc_conv_counts(p, B, plan->ctx) : 0;
-    if (cnt > 0) {
-      if (prod_done) {
-        p.done_in = prod_done;
-        p.done_in_target = prod_target;
-      }
-      p.done_out = counters + (size_t)(n_counting++) * B;
+    int n_units = 0, unit_rows = 0, row_offset = 0, mult = 0;
+    const bool cnt = follow_ok && tc_conv_count_info(p, B, plan->ctx, &n_units, &unit_rows, &row_offset, &mult);
+    TcFollow mine{};
+    if (cnt) {
+      p.follow = prod;                                 // done == nullptr: wait for the whole previous grid
+      p.follow_in_lo = p.src[0].row_base - halo;       // sequence row of staged row 0 at t0 = 0
+      mine = counting(n_units, unit_rows, row_offset, mult, &p.done_out, &p.count_units_per_seg);
     }
     TTSB_CUDA(ln.run(name, layer, 2 * macs, 2.0 * io_elems, [&] { return tc_conv_launch(p, B, plan->ctx, st); }));
-    prod_done = cnt > 0 ? p.done_out : nullptr;
-    prod_target = cnt;
+    prod = mine;
     return 0;
   };
   auto tap = [&](int layer, const __nv_bfloat16* x, int C, int64_t L, bool undo, int x_halo) -> int {
     for (int i = 0; i < a->n_taps; ++i)
       if (a->tap_layers[i] == layer) {
         const CanonDims d = canon_dims(plan, C, L);
-        TTSB_CUDA(tc_untile_launch(x, slab, B, C, L, d.rows, x_halo, undo, slope, a->tap_out[i], st));
+        TTSB_CUDA(tc_untile_launch(x, (int64_t)act_stride(plan, C, L), B, C, L, d.rows, x_halo, undo, slope, a->tap_out[i], st));
       }
     return 0;
   };
@@ -366,6 +385,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   {
     TcConvParams p = base(plan->tc_proj, sh.L0);
     p.src[0] = src(melc, cfg.in_channels, sh.L0, cfg.proj_kernel, 1, -pp, false);
+    cur = fresh(cfg.base_channels, sh.L0);
     canon_out(p, cur, cfg.base_channels, sh.L0, true, 2);
     const double macs = (double)cfg.proj_kernel * cfg.in_channels * cfg.base_channels * sh.L0 * B;
     if (int rc = run("bf16.proj.k7", 1, p, macs,
@@ -392,6 +412,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       // consumer: block 0 (raw x + reflect) or, with no blocks, the next transposed conv / head
       // consumer: the fused stack (mirrors its own edges: no margins), else block 0 (raw x + reflect) or, with
       // no blocks, the next transposed conv / head
+      __nv_bfloat16* nxt = fresh(C, L);
       if (nb > 0) canon_out(p, nxt, C, L, false, stack_tiling(plan, s).kt > 0 ? 0 : 1);
       else canon_out(p, nxt, C, L, true, last_stage ? 1 : 2);
       // a fused stack reads its input at any row offset: shift by a row where that makes the transposed conv's
@@ -402,7 +423,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
       if (int rc = run("bf16.upsample.convT", sp.layer_up, p, macs,
                        (double)B * (sp.Cin * Lin + C * L) + 2.0 * sp.f * sp.Cin * C))
         return rc;
-      std::swap(cur, nxt);
+      cur = nxt;
       if (int rc = tap(sp.layer_up, cur, C, L, nb == 0, cur_halo)) return rc;
     }
     const int half = (cfg.res_kernel - 1) / 2;
@@ -415,7 +436,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     TcStackParams q = stack_tiling(plan, s, fuse_head, fuse_up);
     if (q.kt > 0) {  // whole ResidualStack in one kernel
       const CanonDims din = canon_dims(plan, C, L);
-      q.x = cur; q.x_batch_stride = slab; q.x_plane_rows = din.rows; q.x_halo = cur_halo;
+      q.x = cur; q.x_batch_stride = (int64_t)act_stride(plan, C, L); q.x_plane_rows = din.rows; q.x_halo = cur_halo;
       cur_halo = halo;
       q.L = (int)L; q.slope = slope;
       for (int bi = 0; bi < nb; ++bi) {
@@ -425,17 +446,17 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         q.b1[bi] = Wf + bp.tc_conv1.groups[0].bias_off;
         q.b2s[bi] = Wf + bp.tc_conv2s.groups[0].bias_off;
       }
-      q.out = TcCanonOut{nxt, slab, din.rows, halo, (int)L, 1, last_stage ? 1 : 2};
-      // Follow the previous kernel utterance by utterance when it counted its work.  Several kernels of the chain may
-      // then be in flight; this one writes `nxt`, which an older kernel may still be reading — but only slabs of
-      // utterances this kernel has not reached: it starts utterance b after its producer has finished b, which has
-      // itself waited for ITS producer to finish b, and so on down the chain.
-      const bool follow = follow_ok && prod_done != nullptr;
-      if (follow) {
-        q.done_in = prod_done;
-        q.done_in_target = prod_target;
+      // its output: the next stage's input when the transposed conv rides along, else this stage's stack output
+      // (never written when the head rides along); always a region of its own (see Bf16Workspace)
+      __nv_bfloat16* nxt = fuse_head ? nullptr : fuse_up ? fresh(plan->stages[s + 1].Cout, sh.L[s + 1]) : fresh(C, L);
+      q.out = TcCanonOut{nxt, (int64_t)act_stride(plan, C, L), din.rows, halo, (int)L, 1, last_stage ? 1 : 2};
+      if (follow_ok) q.follow = prod;   // follow the previous kernel segment by segment when it counted its work
+      TcFollow mine{};
+      if (follow_ok) {
+        int n_units = 0, unit_rows = 0, row_offset = 0;
+        tc_stack_count_info(q, &n_units, &unit_rows, &row_offset);
+        mine = counting(n_units, unit_rows, row_offset, 1, &q.done_out, &q.count_units_per_seg);
       }
-      q.done_out = follow_ok ? counters + (size_t)(n_counting++) * B : nullptr;
       double macs = (double)(cfg.res_kernel + 2) * nb * C * C * L * B;
       double bytes = 2.0 * (2.0 * B * C * L + (double)(cfg.res_kernel + 2) * nb * C * C);
       if (fuse_head) {
@@ -450,17 +471,20 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         const CanonDims dn = canon_dims(plan, nx.Cout, sh.L[s + 1]);
         // rows q f - P .. of one GEMM row go out as 32-byte stores: keep (halo - P) even
         cur_halo = halo + ((halo - nx.P) & 1);
-        q.up_out = TcCanonOut{nxt, slab, dn.rows, cur_halo, (int)sh.L[s + 1], 0, 0};
+        q.up_out = TcCanonOut{nxt, (int64_t)act_stride(plan, nx.Cout, sh.L[s + 1]), dn.rows, cur_halo, (int)sh.L[s + 1], 0, 0};
         macs += 2.0 * nx.f * C * nx.Cout * L * B;
         bytes = 2.0 * B * (C * L + (double)nx.Cout * sh.L[s + 1]);
         up_done = true;
       }
       TTSB_CUDA(ln.run(fuse_head ? "bf16.resstack.fused+head" : fuse_up ? "bf16.resstack.fused+convT" : "bf16.resstack.fused",
                        sp.layer_stack, 2 * macs, bytes, [&] { return tc_stack_launch(q, B, plan->ctx, st); }));
-      prod_done = q.done_out;
-      prod_target = q.done_out ? tc_stack_signals_per_utterance(q) : 0;
-      std::swap(cur, nxt);
-    } else
+      prod = mine;
+      cur = nxt;
+    } else {
+    // per-conv fallback: every kernel waits for the whole previous grid, so ping-pong between the stage's input and
+    // one more tensor of the same shape is safe; h goes to a scratch tensor
+    __nv_bfloat16* nxt = nb > 0 ? fresh(C, L) : nullptr;
+    __nv_bfloat16* hbuf = act + wsz.act_elems - (size_t)B * act_stride(plan, C, L);   // the scratch region is the largest
     for (int bi = 0; bi < nb; ++bi) {
       const BlockPlan& bp = sp.blocks[bi];
       const int d = bp.dilation;
@@ -486,6 +510,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         std::swap(cur, nxt);
       }
     }
+    }
     if (nb > 0)
       if (int rc = tap(sp.layer_stack, cur, C, L, true, halo)) return rc;
     Lin = L;
@@ -505,7 +530,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     }
     if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
     // the PQMF kernel follows a counting head kernel utterance by utterance
-    if (int rc = finish_output(plan, a, ln, dst, to_out, Lin, head_done ? prod_done : nullptr, prod_target)) return rc;
+    if (int rc = finish_output(plan, a, ln, dst, to_out, Lin, head_done && prod.done ? &prod : nullptr)) return rc;
   }
   return 0;
 }

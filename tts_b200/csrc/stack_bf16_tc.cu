@@ -220,24 +220,20 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   pdl_launch_dependents();
   // With done_in the previous kernel is followed utterance by utterance (the loader polls its counters) and nobody
   // waits for its whole grid; what this kernel writes is then never a buffer the previous kernel still reads.
-  const bool follow = p.done_in != nullptr;
+  const bool follow = p.follow.done != nullptr;
   if (warp != PRODUCER_WARP && !follow) pdl_wait();   // the producer first prefetches weights (not written by any kernel)
 
   if (warp == PRODUCER_WARP) {
     // =============================== producer ===============================
     if (elect_one()) {
-      int ready_b = -1;   // utterances up to here are complete in the previous kernel (follow mode)
+      FollowState fst;   // which segments of the previous kernel's output are known complete (follow mode)
       auto load_x = [&](int it) {
         const int item = blockIdx.x + it * gridDim.x;
         if (item >= n_items) return;
         const int buf = it & 1;
         if (it >= 2) mbar_wait(&bars.x_free[buf], ((it >> 1) - 1) & 1);
         const int b = item / p.n_chains, chain = item - b * p.n_chains;
-        if (follow && b > ready_b) {
-          wait_counter(p.done_in + b, p.done_in_target);
-          fence_proxy_async_global();
-          ready_b = b;
-        }
+        if (follow) follow_wait(p.follow, b, chain * V - SD, chain * V - SD + TR, fst);
         const int g0 = chain * V - SD;
         mbar_expect_tx(&bars.x_full[buf], (uint32_t)PL * TR * 16);
         const __nv_bfloat16* gx = p.x + (int64_t)b * p.x_batch_stride + (int64_t)(p.x_halo + g0) * 8;
@@ -621,10 +617,11 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     // that counter (wait_counter) instead of waiting for this whole grid.
     if (p.done_out && elect_one()) {
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
-        const int b = (blockIdx.x + it * gridDim.x) / p.n_chains;
+        const int item = blockIdx.x + it * gridDim.x;
+        const int b = item / p.n_chains, chain = item - b * p.n_chains;
         mbar_wait(&bars.item_done, it & 1);
         __threadfence();
-        atomicAdd(p.done_out + b, 1);
+        atomicAdd(p.done_out + b * FOLLOW_SEGS + chain / p.count_units_per_seg, 1);
       }
     }
   } else {
@@ -1279,9 +1276,13 @@ size_t tc_stack_smem_bytes(const TcStackParams& p) {
          (p.up_w && p.up_mode == 1 ? (size_t)2 * p.cp * p.up_n * 2 : 0);
 }
 
-int tc_stack_signals_per_utterance(const TcStackParams& p) {
+void tc_stack_count_info(const TcStackParams& p, int* n_units, int* unit_rows, int* row_offset) {
   const int V = p.kt * 128 - 2 * (p.sum_d + (p.head_w ? (p.head_taps - 1) / 2 : p.up_w ? 1 : 0));
-  return ceil_div(p.L + (p.up_w ? 1 : 0), V);   // one count per finished chain
+  *n_units = ceil_div(p.L + (p.up_w ? 1 : 0), V);   // chains per utterance
+  // chain c owns GEMM rows [c V, (c + 1) V); with the fused transposed conv they become output rows
+  // [c V f - P, (c + 1) V f - P)
+  *unit_rows = V * (p.up_w ? p.up_f : 1);
+  *row_offset = p.up_w ? p.up_P : 0;
 }
 
 cudaError_t tc_stack_launch(const TcStackParams& p_in, int batch, const TcLaunchCtx& ctx, cudaStream_t stream) {

@@ -94,21 +94,6 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
   }
 }
 
-// ---- cross-kernel hand-over without waiting for the whole producer grid -----------------------------------------
-// A producer kernel counts finished work items per utterance in global memory (stores -> __syncwarp -> lane 0:
-// __threadfence + atomicAdd); a consumer launched behind it with programmatic dependent launch polls the counter
-// with an acquire load instead of griddepcontrol.wait, so it starts on the SMs the producer's tail has left idle.
-// Bulk copies read through the async proxy: the proxy fence orders them behind the acquire.
-__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
-__device__ __forceinline__ void wait_counter(const int* p, int target) {
-  while (ld_acquire_gpu(p) < target) __nanosleep(64);
-}
-
 // ---- bulk async copy global -> shared (TMA engine, no tensor map) -------------------------------
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(

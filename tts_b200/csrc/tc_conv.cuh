@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "follow.cuh"
+
 namespace ttsb {
 
 // Device facts and debug knobs of a plan, read ONCE at plan creation: nothing on the launch path queries the
@@ -73,12 +75,14 @@ struct TcConvParams {
   float* out_f;           // fp32 NCL out [B][cout_real][out_L]
   int cout_real;
   float slope;
-  // Hand-over per utterance (tc_common.cuh wait_counter; persistent kernel only — tc_conv_counts()): done_out[b] += 1
-  // per finished (time tile, column group) of utterance b; with done_in the loaders poll the previous kernel's
-  // counters instead of the kernel waiting for that whole grid.
+  // Hand-over per time segment (follow.cuh; persistent kernel only — tc_conv_count_info()): every CTA counts its
+  // finished time tiles in done_out[b][tile / count_units_per_seg]; with follow.done the loaders poll the previous
+  // kernel's counters instead of the kernel waiting for that whole grid.  follow_in_lo: sequence row of the first
+  // staged input row of GEMM row 0 (min tap shift).
   int* done_out;
-  const int* done_in;
-  int done_in_target;
+  int count_units_per_seg;
+  TcFollow follow;
+  int follow_in_lo;
   long long* trace;       // optional timeline buffer (trace.cuh)
   int trace_id;
   int debug;              // knock-out bits for timeline experiments (trace builds only)
@@ -138,12 +142,12 @@ struct TcStackParams {
   int up_f, up_P, up_n;          // stride, output offset (padding), GEMM columns = f * C_next_pad
   int up_mode;                   // filled by tc_stack_configure: 1 weights resident, 2 streamed through the W2S slot
   TcCanonOut up_out;             // raw input of the next stage's stack (no margins), L = next length
-  // Hand-over between consecutive kernels per utterance instead of per grid (tc_common.cuh wait_counter):
-  // done_out[b] += 1 per finished item (chain) of utterance b; with done_in the kernel skips
-  // griddepcontrol.wait and its loader waits for done_in[b] >= done_in_target before the first load of utterance b.
+  // Hand-over between consecutive kernels per time segment instead of per grid (follow.cuh): the signal warp counts
+  // finished chains in done_out[b][chain / count_units_per_seg]; with follow.done the kernel skips
+  // griddepcontrol.wait and its loader waits for the segments that cover the rows of the item it is about to load.
   int* done_out;
-  const int* done_in;
-  int done_in_target;
+  int count_units_per_seg;
+  TcFollow follow;
   int debug;               // knock-out bits for timeline experiments (trace builds only)
   long long* trace;        // optional (TTSB200_STACK_TRACE): [role][256] {tag, clock} pairs written by CTA 0
   TcCanonOut out;
@@ -155,13 +159,16 @@ int tc_stack_cs(int cp);                          // epilogue warps per TMEM lan
 bool tc_stack_configure(TcStackParams& p);        // fills kt / sum_d / guard / w_sets from cp, dil[], nblocks
 size_t tc_stack_smem_bytes(const TcStackParams& p);
 cudaError_t tc_stack_launch(const TcStackParams& p, int batch, const TcLaunchCtx& ctx, cudaStream_t stream);
-int tc_stack_signals_per_utterance(const TcStackParams& p);   // what done_out[b] reaches when utterance b is complete
+// What a consumer of this launch's output needs to follow it: work units (chains) per utterance, output rows per
+// unit and the row offset (follow.cuh TcFollow).
+void tc_stack_count_info(const TcStackParams& p, int* n_units, int* unit_rows, int* row_offset);
 
 size_t tc_conv_smem_bytes(const TcConvParams& p);
 // True when tc_conv_launch will run this launch on the persistent weights-resident kernel, the one that counts
-// finished work per utterance (done_out) and can follow a counting producer (done_in); 0 otherwise.  The value is what
-// done_out[b] reaches when utterance b is complete.
-int tc_conv_counts(const TcConvParams& p, int batch, const TcLaunchCtx& ctx);
+// finished work (done_out) and can follow a counting producer (follow.done); fills what a consumer needs (TcFollow):
+// time tiles per utterance, output rows per tile, row offset, counts per tile (column groups).
+bool tc_conv_count_info(const TcConvParams& p, int batch, const TcLaunchCtx& ctx, int* n_units, int* unit_rows,
+                        int* row_offset, int* mult);
 cudaError_t tc_conv_launch(const TcConvParams& p, int batch, const TcLaunchCtx& ctx, cudaStream_t stream);
 
 // mel fp32 [B][C][T] -> canonical bf16 with replicate padding `pad` folded in and reflect margins

@@ -177,7 +177,7 @@ int copy_tap(const ttsb200_forward_args* a, int layer, const float* src, int C, 
 // result (no PQMF / skip_pqmf, fp32 out), or it is converted to fp16, or PQMF synthesis turns it into the waveform
 // (the synthesis kernels store fp32 or fp16 themselves).
 int finish_output(const ttsb200_plan* plan, const ttsb200_forward_args* a, Launcher& ln, const float* sub, bool to_out,
-                  int64_t Lin, const int* done_in = nullptr, int done_target = 0) {
+                  int64_t Lin, const TcFollow* follow = nullptr) {
   const ttsb200_generator_config& cfg = plan->cfg;
   const int B = a->batch;
   const int f16 = a->out_dtype == TTSB200_OUT_F16;
@@ -207,7 +207,7 @@ int finish_output(const ttsb200_plan* plan, const ttsb200_forward_args* a, Launc
                    4.0 * N * Lin * B + (f16 ? 2.0 : 4.0) * out_samples, [&] {
     if (plan->pqmf_fact && !plan->ctx.pqmf_direct && pqmf_fact_usable(sub, Lin))
       return pqmf_synthesis_fact_launch(sub, plan->blob + plan->pqmf_fact_off, B, Lin, a->out, f16,
-                                        windowed ? &crop : nullptr, done_in, done_target, st);
+                                        windowed ? &crop : nullptr, follow, st);
     return pqmf_synthesis_launch(sub, plan->blob + plan->pqmf_G_off, B, N, cfg.pqmf_taps, Lin, a->out, f16,
                                  windowed ? &crop : nullptr, st);
   }));
