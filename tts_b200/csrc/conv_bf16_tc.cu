@@ -808,10 +808,21 @@ __global__ void __launch_bounds__(NTS) tc_convs_kernel(const __grid_constant__ T
 __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int pad, __nv_bfloat16* __restrict__ out,
                                 int planes, int plane_rows, int halo, int* __restrict__ counters, int n_counters) {
   // one thread per (plane row, plane); row index covers halo margins too (reflect of the padded signal)
-  pdl_launch_dependents();
+  //
+  // Hand-over counters (follow.cuh): block 0 zeroes them once the previous inference has completed, and only THEN
+  // lets the dependent kernels launch (a dependent launches when every CTA of this grid has triggered).  Without that
+  // order the next kernels — programmatic dependent launches cascade, so with small grids a whole inference can be
+  // resident while the previous one drains — would poll the previous inference's final counts, take them for their
+  // producer's and read tensors that have not been written yet.
+  const bool zeroes = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+  if (!zeroes) pdl_launch_dependents();
   pdl_wait();
-  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0)
+  if (zeroes) {
     for (int i = threadIdx.x; i < n_counters; i += blockDim.x) counters[i] = 0;
+    __threadfence();
+    __syncthreads();
+    pdl_launch_dependents();
+  }
   const int L = T + 2 * pad;
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   const int pl = blockIdx.y, b = blockIdx.z;

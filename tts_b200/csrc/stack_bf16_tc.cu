@@ -88,10 +88,18 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   constexpr int KS = CP / 16;         // K = 16 steps per tap
   constexpr int TR = KT * 128;        // staged rows owned by the chain
   constexpr int CW = CP / CS;         // channels per epilogue thread
-  constexpr int TCOLS = 5 * CP / 2;   // TMEM columns per tile: D1 | D2 | XR
+  // C = 256: D1 | D2 alone are the 512 TMEM columns.  Raw x then lives INSIDE D1, in its upper half (h takes the
+  // lower one): the shortcut MMAs, which read it, are issued before the block's dilated conv, which overwrites it —
+  // one issuer, so they execute in that order.  The D1 bias cannot be pre-loaded then (it would wipe x): the first
+  // conv MMA overwrites and epilogue 1 adds the bias.  One XA buffer (two would leave no room for the weight ring).
+  constexpr bool OVERLAY = CP > 192;
+  constexpr int TCOLS = OVERLAY ? 2 * CP : 5 * CP / 2;   // TMEM columns per tile: D1 | D2 | XR
+  constexpr int XR_OFF = OVERLAY ? CP / 2 : 2 * CP;      // column of raw x (bf16, CP / 2 columns) within the tile
+  constexpr int NXA = OVERLAY ? 1 : 2;                   // staged x tiles
   constexpr int ONES_COL = KT * TCOLS;   // 8 columns behind the tiles: the constant A operand of the bias MMAs
-  static_assert(KT * TCOLS + 8 <= 512, "TMEM budget");
-  constexpr uint32_t TMEM_ALLOC = KT * TCOLS + 8 <= 128 ? 128 : KT * TCOLS + 8 <= 256 ? 256 : 512;   // <= 256: two CTAs share an SM
+  constexpr int ONES_W = CP > 96 ? 0 : 8;                // ring mode has no bias MMAs
+  static_assert(KT * TCOLS + ONES_W <= 512, "TMEM budget");
+  constexpr uint32_t TMEM_ALLOC = KT * TCOLS + ONES_W <= 128 ? 128 : KT * TCOLS + ONES_W <= 256 ? 256 : 512;   // <= 256: two CTAs share an SM
   static_assert(CW % 8 == 0, "CP must be a multiple of 16");
   // Ring mode (wide stages, one tile per CTA): a block's weights do not fit in shared memory, so they stream
   // through a ring of [RING_KB channels x CP columns] chunks in exactly the order the MMAs consume them.
@@ -137,7 +145,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   constexpr uint32_t W1_BYTES = TAPS * CP * CP * 2, W2_BYTES = 2 * CP * CP * 2;
   const int wsets = p.w_sets;  // nb: every block's weights stay resident; 1: reloaded per block; ring mode: slots
   uint8_t* sXA = smem;
-  uint8_t* sW = smem + 2 * xa_bytes;   // [set][W1 | W2S]
+  uint8_t* sW = smem + NXA * xa_bytes;   // [set][W1 | W2S]
   uint8_t* sWH = sW + (RING ? (size_t)wsets * SLOT_BYTES : (size_t)wsets * (W1_BYTES + W2_BYTES));   // head weights
   const uint32_t wh_bytes = head ? (uint32_t)CP * p.head_n * 2 : 0;
   // Bias operands (B of the bias MMAs): per block {b1, b2 + bs} as [CP rows x 16 B] planes (K-rows 0/1 = hi/lo), the
@@ -158,6 +166,19 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   };
 
   const int n_items = p.n_chains * p.batch;
+  auto xbuf = [](int it) { return NXA == 2 ? (it & 1) : 0; };               // which staged x tile item `it` uses
+  auto xpar = [](int it) { return NXA == 2 ? ((it >> 1) & 1) : (it & 1); };  // phase parity of its x_full / x_free
+  // Ring mode: global address of chunk `ch` of block `blk` in the order the MMAs consume them — dilated conv, W2, S;
+  // with raw x inside D1 (OVERLAY) the shortcut S goes first.  p.w2s[blk] = [W2 | S].
+  auto ring_src = [&](int blk, int ch) -> const __nv_bfloat16* {
+    constexpr int NKc = CP / RING_KB;
+    constexpr size_t CH = (size_t)RING_KB * CP;   // elements per chunk
+    if (!OVERLAY)
+      return ch < TAPS * NKc ? p.w1[blk] + (size_t)ch * CH : p.w2s[blk] + (size_t)(ch - TAPS * NKc) * CH;
+    if (ch < NKc) return p.w2s[blk] + (size_t)(NKc + ch) * CH;
+    if (ch < NKc + TAPS * NKc) return p.w1[blk] + (size_t)(ch - NKc) * CH;
+    return p.w2s[blk] + (size_t)(ch - NKc - TAPS * NKc) * CH;
+  };
 
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
@@ -230,8 +251,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       auto load_x = [&](int it) {
         const int item = blockIdx.x + it * gridDim.x;
         if (item >= n_items) return;
-        const int buf = it & 1;
-        if (it >= 2) mbar_wait(&bars.x_free[buf], ((it >> 1) - 1) & 1);
+        const int buf = xbuf(it);
+        if (it >= NXA) mbar_wait(&bars.x_free[buf], xpar(it - NXA));
         const int b = item / p.n_chains, chain = item - b * p.n_chains;
         if (follow) follow_wait(p.follow, b, chain * V - SD, chain * V - SD + TR, fst);
         const int g0 = chain * V - SD;
@@ -265,15 +286,15 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           if (RING) {
             for (int ch = 0; ch < NCH; ++ch) {
               const uint32_t gc = (uint32_t)gb * NCH + ch;          // global chunk counter
-              if (blk == 0 && ch == 0) load_x(it + 1);
+              if (NXA == 2 && blk == 0 && ch == 0) load_x(it + 1);
               if (gc & 1) continue;                                 // odd chunks: the second producer warp
               const int slot = gc % wsets;
               mbar_wait(&bars.ring_empty[slot], ((gc / wsets) & 1) ^ 1);
               mbar_expect_tx(&bars.ring_full[slot], SLOT_BYTES);
-              const __nv_bfloat16* src = ch < TAPS * NK ? p.w1[blk] + (size_t)ch * (SLOT_BYTES / 2)
-                                                        : p.w2s[blk] + (size_t)(ch - TAPS * NK) * (SLOT_BYTES / 2);
-              bulk_g2s(sW + (size_t)slot * SLOT_BYTES, src, SLOT_BYTES, &bars.ring_full[slot]);
+              bulk_g2s(sW + (size_t)slot * SLOT_BYTES, ring_src(blk, ch), SLOT_BYTES, &bars.ring_full[slot]);
             }
+            // one x buffer: the next tile can only come in once this item's last dilated conv has read the old one
+            if (NXA == 1 && blk == nb - 1) load_x(it + 1);
             continue;
           }
           if (wsets == 1 || it == 0) {
@@ -305,9 +326,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             const int slot = gc % wsets;
             mbar_wait(&bars.ring_empty[slot], ((gc / wsets) & 1) ^ 1);
             mbar_expect_tx(&bars.ring_full[slot], SLOT_BYTES);
-            const __nv_bfloat16* src = ch < TAPS * NK ? p.w1[blk] + (size_t)ch * (SLOT_BYTES / 2)
-                                                      : p.w2s[blk] + (size_t)(ch - TAPS * NK) * (SLOT_BYTES / 2);
-            bulk_g2s(sW + (size_t)slot * SLOT_BYTES, src, SLOT_BYTES, &bars.ring_full[slot]);
+            bulk_g2s(sW + (size_t)slot * SLOT_BYTES, ring_src(blk, ch), SLOT_BYTES, &bars.ring_full[slot]);
           }
     }
   } else if (RING && warp == MMA_WARP) {
@@ -322,15 +341,37 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     const uint64_t a_tmpl = make_desc(0, lbo_a, 128), b_tmpl = make_desc(0, LBO_B, 128);
     int gb = 0;
     for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
-      const int buf = it & 1;
+      const int buf = xbuf(it);
       const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
       for (int blk = 0; blk < nb; ++blk, ++gb) {
         const uint32_t ph = gb & 1;
         const int d = p.dil[blk];
+        uint32_t gc = (uint32_t)gb * NCH;
+        // NK chunks of A-from-TMEM MMAs into D2: the 1x1 conv on h (A at column 0) or the shortcut on raw x (XR_OFF)
+        auto ts_round = [&](uint32_t a_col0) {
+          for (int kc = 0; kc < NK; ++kc, ++gc) {
+            const int slot = gc % wsets;
+            mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
+            tc_fence_after();
+            if (leader) {
+              const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
+              const uint32_t acol = a_col0 + 8 * (kc * (RING_KB / 16));
+#pragma unroll
+              for (int kk = 0; kk < RING_KB / 16; ++kk)
+                umma_bf16_ts(tbase + CP, acol + 8 * kk, b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
+              umma_commit(&bars.ring_empty[slot]);
+            }
+            __syncwarp();
+          }
+        };
+        if (OVERLAY) {   // the shortcut first: raw x sits where the dilated conv is about to accumulate
+          mbar_wait(&bars.xr_ready[0], ph);
+          tc_fence_after();
+          ts_round(tbase + XR_OFF);
+        }
         // ---- dilated conv: D1 = sum_tap XA[rows + (tap-1) d] W1[tap]^T
         mbar_wait(&bars.xa_ready[0], ph);
         tc_fence_after();
-        uint32_t gc = (uint32_t)gb * NCH;
         for (int j = 0; j < TAPS; ++j) {
           const uint32_t a_row = xa + (uint32_t)(G + (j - 1) * d) * 16;
           for (int kc = 0; kc < NK; ++kc, ++gc) {
@@ -342,7 +383,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
 #pragma unroll
               for (int kk = 0; kk < RING_KB / 16; ++kk)
                 umma_bf16(tbase, a_tmpl | (uint64_t)((a_row + (uint32_t)(kc * (RING_KB / 8) + 2 * kk) * lbo_a) >> 4),
-                          b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
+                          b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc,
+                          OVERLAY ? (uint32_t)(j + kc + kk > 0) : 1u);   // OVERLAY: D1 holds no bias row, the first MMA overwrites
               umma_commit(&bars.ring_empty[slot]);
             }
             __syncwarp();
@@ -353,25 +395,12 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           if (blk == nb - 1) umma_commit(&bars.x_free[buf]);
         }
         __syncwarp();
-        // ---- 1x1 conv on h + 1x1 shortcut on raw x, both A operands in TMEM
+        // ---- 1x1 conv on h (+ 1x1 shortcut on raw x), A operands in TMEM
         mbar_wait(&bars.h_ready[0], ph);
-        if (SPLIT_E2) mbar_wait(&bars.xr_ready[0], ph);
+        if (SPLIT_E2 && !OVERLAY) mbar_wait(&bars.xr_ready[0], ph);
         tc_fence_after();
-        for (int sx = 0; sx < 2; ++sx)
-          for (int kc = 0; kc < NK; ++kc, ++gc) {
-            const int slot = gc % wsets;
-            mbar_wait(&bars.ring_full[slot], (gc / wsets) & 1);
-            tc_fence_after();
-            if (leader) {
-              const uint32_t wb = smem_u32(sW + (size_t)slot * SLOT_BYTES);
-              const uint32_t acol = tbase + (sx ? 2 * CP : 0) + 8 * (kc * (RING_KB / 16));
-#pragma unroll
-              for (int kk = 0; kk < RING_KB / 16; ++kk)
-                umma_bf16_ts(tbase + CP, acol + 8 * kk, b_tmpl | (uint64_t)((wb + 2 * kk * LBO_B) >> 4), idesc, 1);
-              umma_commit(&bars.ring_empty[slot]);
-            }
-            __syncwarp();
-          }
+        ts_round(tbase);
+        if (!OVERLAY) ts_round(tbase + XR_OFF);
         if (leader) umma_commit(&bars.d2_full[0]);
         __syncwarp();
       }
@@ -397,7 +426,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     int gb = 0;
     uint32_t n_xa = 0;   // completed xa_ready rounds (one per block, plus one per item with a fused tail conv)
     for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
-      const int buf = it & 1;
+      const int buf = xbuf(it);
       const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
       for (int blk = 0; blk < nb; ++blk, ++gb) {
         const int set = wsets == 1 ? 0 : blk;
@@ -499,7 +528,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     uint32_t n_xa = 0;   // same count as the conv issuer's
     uint32_t n_w2 = 0;   // consumed fills of the streamed W2S slot
     for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
-      const int buf = it & 1;
+      const int buf = xbuf(it);
       const uint32_t xa = smem_u32(sXA + (size_t)buf * xa_bytes);
       for (int blk = 0; blk < nb; ++blk, ++gb) {
         const uint32_t ph = gb & 1;
@@ -520,7 +549,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             umma_bf16_ts(tcol + CP, tbase + ONES_COL, b2_desc, idesc, 0);   // D2[t] <- b2 + bs (overwrites)
 #pragma unroll
             for (int kk = 0; kk < KS; ++kk)
-              umma_bf16_ts(tcol + CP, tcol + 2 * CP + 8 * kk,
+              umma_bf16_ts(tcol + CP, tcol + XR_OFF + 8 * kk,
                            b_tmpl | (uint64_t)((w2 + CP * CP * 2 + 2 * kk * LBO_B) >> 4), idesc, 1);
           }
           __syncwarp();
@@ -564,7 +593,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           if (leader) {
 #pragma unroll
             for (int kk = 0; kk < KS; ++kk)
-              umma_bf16_ts(tcol, tcol + 2 * CP + 8 * kk, bh_tmpl | (uint64_t)((wh + 2 * kk * lbo_h) >> 4), idesc_h,
+              umma_bf16_ts(tcol, tcol + XR_OFF + 8 * kk, bh_tmpl | (uint64_t)((wh + 2 * kk * lbo_h) >> 4), idesc_h,
                            kk > 0);
             umma_commit(&bars.d1_full[t]);
           }
@@ -655,10 +684,10 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       const int item_ = blockIdx.x + it_ * gridDim.x;
       const int b_ = item_ / p.n_chains, chain_ = item_ - b_ * p.n_chains;
       const int g0_ = chain_ * V - SD;
-      uint8_t* xa_ = sXA + (size_t)(it_ & 1) * xa_bytes + (size_t)(c0 / 8) * plane_bytes;
+      uint8_t* xa_ = sXA + (size_t)xbuf(it_) * xa_bytes + (size_t)(c0 / 8) * plane_bytes;
       const int reach_ = G > p.out.halo ? G : p.out.halo;
       const bool edge_ = g0_ <= reach_ || g0_ + TR + reach_ >= L - 1;
-      mbar_wait_relaxed(&bars.x_full[it_ & 1], (it_ >> 1) & 1);
+      mbar_wait_relaxed(&bars.x_full[xbuf(it_)], xpar(it_));
       uint32_t w[CW / 2];
       const uint8_t* src = xa_ + (size_t)(G + t * 128 + m) * 16;
 #pragma unroll
@@ -666,7 +695,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         const uint4 u = *reinterpret_cast<const uint4*>(src + (size_t)pl * plane_bytes);
         w[4 * pl] = u.x; w[4 * pl + 1] = u.y; w[4 * pl + 2] = u.z; w[4 * pl + 3] = u.w;
       }
-      tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+      tmem_st<CW / 2>(tlane + XR_OFF + c0 / 2, w);
 #pragma unroll
       for (int i = 0; i < CW / 2; ++i) w[i] = lrelu_bf16x2(w[i], slope2);
       auto rows = [&](int r) {
@@ -699,7 +728,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     int gb = 0;
     for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
       const int item = blockIdx.x + it * gridDim.x;
-      const int buf = it & 1;
+      const int buf = xbuf(it);
       const int b = item / p.n_chains, chain = item - b * p.n_chains;
       const int g0 = chain * V - SD;            // sequence row of staged row 0
       uint8_t* xa = sXA + (size_t)buf * xa_bytes + (size_t)(c0 / 8) * plane_bytes;   // this thread's first plane
@@ -830,7 +859,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         if (SPLIT_E2) mbar_arrive(&bars.xr_ready[t]);
         tr(201);
       } else {
-      mbar_wait_relaxed(&bars.x_full[buf], (it >> 1) & 1);
+      mbar_wait_relaxed(&bars.x_full[buf], xpar(it));
       tr(200);
       {
         uint32_t w[CW / 2];
@@ -841,8 +870,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           w[4 * pl] = u.x; w[4 * pl + 1] = u.y; w[4 * pl + 2] = u.z; w[4 * pl + 3] = u.w;
         }
         // critical half first (what the dilated conv needs), then raw x for the 1x1 shortcut
-        if (!BIAS_MMA) init_acc(tlane, s_bias[0][0]);
-        if (!SPLIT_E2) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+        if (!BIAS_MMA && !OVERLAY) init_acc(tlane, s_bias[0][0]);
+        if (!SPLIT_E2) tmem_st<CW / 2>(tlane + XR_OFF + c0 / 2, w);
         uint32_t a[CW / 2];
 #pragma unroll
         for (int i = 0; i < CW / 2; ++i) a[i] = lrelu_bf16x2(w[i], slope2);
@@ -852,7 +881,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         tc_fence_before();
         mbar_arrive(&bars.xa_ready[t]);
         if (SPLIT_E2) {
-          tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+          tmem_st<CW / 2>(tlane + XR_OFF + c0 / 2, w);
           if (!BIAS_MMA) init_acc(tlane + CP, s_bias[0][1]);
           tmem_wait_st();
           tc_fence_before();
@@ -871,11 +900,32 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
           tc_fence_after();
           tr(210);
           trw(310);
+          uint32_t w[CW / 2];
+          if (OVERLAY) {
+            // D1 carries no bias row (raw x lived in its upper half): add b1 here; 16 columns at a time with the next
+            // TMEM load in flight, so that 64 channels per thread do not need 64 + 32 live registers
+            uint32_t v[2][16];
+            tmem_ld16_nw(tlane + c0, v[0]);
+#pragma unroll
+            for (int c = 0; c < CW; c += 16) {
+              uint32_t* vc = v[(c / 16) & 1];
+              tmem_wait_ld();
+              if (c + 16 < CW) tmem_ld16_nw(tlane + c0 + c + 16, v[((c / 16) & 1) ^ 1]);
+              const float4* bb = reinterpret_cast<const float4*>(&s_bias[RING ? blk : 0][0][RING ? c0 + c : 0]);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float4 b4 = bb[i];
+                w[c / 2 + 2 * i] = pack_bf16x2(lrelu_f(__uint_as_float(vc[4 * i]) + b4.x, slope),
+                                               lrelu_f(__uint_as_float(vc[4 * i + 1]) + b4.y, slope));
+                w[c / 2 + 2 * i + 1] = pack_bf16x2(lrelu_f(__uint_as_float(vc[4 * i + 2]) + b4.z, slope),
+                                                   lrelu_f(__uint_as_float(vc[4 * i + 3]) + b4.w, slope));
+              }
+            }
+          } else {
           uint32_t v[CW];
           tmem_ld_nw<CW>(tlane + c0, v);
           tmem_wait_ld();
           tr(212);
-          uint32_t w[CW / 2];
           if (DBG(64)) {
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = v[i];
@@ -883,6 +933,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i)
               w[i] = pack_bf16x2(lrelu_f(__uint_as_float(v[2 * i]), slope), lrelu_f(__uint_as_float(v[2 * i + 1]), slope));
+          }
           }
           tr(213);
           // every warp of the quarter must have read D1 before any of them overwrites its low columns
@@ -921,8 +972,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
               for (int i = 0; i < 8; ++i) a8[i] = lrelu_bf16x2(w8[i], slope2);
               xa_store16(c, a8, last && up);
               if (!last) {
-                tmem_st8(tlane + 2 * CP + (c0 + c) / 2, w8);
-                if (!BIAS_MMA) init_acc16(tlane, s_bias[RING ? blk + 1 : 0][0], c);
+                tmem_st8(tlane + XR_OFF + (c0 + c) / 2, w8);
+                if (!BIAS_MMA && !OVERLAY) init_acc16(tlane, s_bias[RING ? blk + 1 : 0][0], c);
               }
             }
             tr(225);
@@ -950,12 +1001,12 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             tr(223);
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) w[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-            if (!SPLIT_E2 && !last && !DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+            if (!SPLIT_E2 && !last && !DBG(2)) tmem_st<CW / 2>(tlane + XR_OFF + c0 / 2, w);
             uint32_t a[CW / 2];
 #pragma unroll
             for (int i = 0; i < CW / 2; ++i) a[i] = DBG(32) ? w[i] : lrelu_bf16x2(w[i], slope2);
             tr(224);
-            if (last && head) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, a);   // A operand of the fused head (TMEM)
+            if (last && head) tmem_st<CW / 2>(tlane + XR_OFF + c0 / 2, a);   // A operand of the fused head (TMEM)
             else if (last && up) put_xa_up(a);
             else put_xa(a);
             tr(225);
@@ -967,7 +1018,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
             tr(221);
             trw(321);
             if (SPLIT_E2 && !last) {
-              if (!DBG(2)) tmem_st<CW / 2>(tlane + 2 * CP + c0 / 2, w);
+              if (!DBG(2)) tmem_st<CW / 2>(tlane + XR_OFF + c0 / 2, w);
               tmem_wait_st();
               tc_fence_before();
               mbar_arrive(&bars.xr_ready[t]);
@@ -1168,7 +1219,12 @@ cudaError_t launch(const TcStackParams& p, size_t smem, int grid, int device, cu
   static std::atomic<uint64_t> attr_done{0};
   const uint64_t bit = 1ull << (device & 63);
   if (!(attr_done.load(std::memory_order_acquire) & bit)) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    // dynamic + static shared memory share the 227 KB of a CTA: the C = 256 instantiation carries 8 KB of fp32 bias rows
+    cudaFuncAttributes fa{};
+    cudaError_t e = cudaFuncGetAttributes(&fa, kern);
+    if (e != cudaSuccess) return e;
+    const int dyn_max = std::min<int>((int)SMEM_MAX, 227 * 1024 - (int)fa.sharedSizeBytes);
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max);
     if (e != cudaSuccess) return e;
     attr_done.fetch_or(bit, std::memory_order_release);
   }
@@ -1189,6 +1245,7 @@ int tc_stack_kt(int cp) {
   static int cache[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};   // cp -> kt, filled on first use per cp
   int dflt;
   switch (cp) {
+    case 256: return 1;
     case 192: return 1;
     case 128: return 1;
     case 96: return 2;
@@ -1237,7 +1294,7 @@ bool tc_stack_configure(TcStackParams& p) {
   const int hh = head ? (p.head_taps - 1) / 2 : up ? 1 : 0;
   if (hh > p.guard) p.guard = (hh + 7) / 8 * 8;
   if (p.kt * 128 - 2 * (p.sum_d + hh) < 32 || p.guard + p.sum_d + hh > 127) return false;
-  const size_t xa = 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;
+  const size_t xa = (p.cp > 192 ? 1 : 2) * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16;   // C = 256: one x tile
   const size_t wset = (size_t)(TAPS + 2) * p.cp * p.cp * 2;
   const size_t wh = head_smem_bytes(p) + bias_smem_bytes(p);
   // two CTAs per SM when the TMEM footprint allows it: each then gets half of the shared memory
@@ -1268,8 +1325,8 @@ cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, int device, 
 
 size_t tc_stack_smem_bytes(const TcStackParams& p) {
   if (p.cp > 96)
-    return 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 + (size_t)p.w_sets * RING_KB * p.cp * 2 +
-           bias_smem_bytes(p);
+    return (p.cp > 192 ? 1 : 2) * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 +
+           (size_t)p.w_sets * RING_KB * p.cp * 2 + bias_smem_bytes(p);
   return bias_smem_bytes(p) + 2 * (size_t)(p.cp / 8) * (p.kt * 128 + 2 * p.guard) * 16 +
          (size_t)p.w_sets * (TAPS + 2) * p.cp * p.cp * 2 +
          head_smem_bytes(p) +
@@ -1309,6 +1366,7 @@ cudaError_t dispatch(const TcStackParams& p, size_t smem, int grid, int device, 
   const int tail = p.head_w ? 1 : p.up_w ? 2 : 0;
 #define TTSB_STACK_CASE(CP, KT, CS, TAIL) \
   if (p.cp == CP && p.kt == KT && tail == TAIL) return launch<CP, KT, CS, TAIL>(p, smem, grid, device, stream)
+  TTSB_STACK_CASE(256, 1, 4, 0);
   TTSB_STACK_CASE(192, 1, 4, 0);
   TTSB_STACK_CASE(128, 1, 4, 0);
   TTSB_STACK_CASE(96, 2, 2, 0);
