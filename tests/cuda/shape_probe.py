@@ -1,12 +1,12 @@
 """Per-kernel times and back-to-back step time of one inference shape (debug aid):
-    python tests/cuda/shape_probe.py B T [steps]"""
+    python tests/cuda/shape_probe.py B T [steps] [generator class]"""
 import os, sys, torch
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
 import bench
 from tts_b200.engine import Profile
 B, T = int(sys.argv[1]), int(sys.argv[2])
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 50
-m = bench.make_model("bf16").to("cuda").eval(); m.freeze()
+m = bench.make_model("bf16", *(sys.argv[4:5])).to("cuda").eval(); m.freeze()
 mel = torch.randn(B, 80, T, device="cuda")
 for _ in range(5): m.inference(mel)
 torch.cuda.synchronize()

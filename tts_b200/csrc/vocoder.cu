@@ -2,6 +2,8 @@
 // generator.inference(), per-launch profiling and the host-buffer entry point.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -418,6 +420,15 @@ int32_t ttsb200_plan_create(const ttsb200_generator_config* cfg, const float* co
   }
   plan->blob_floats = bb.data.size();
   plan->blob16_elems = b16.data.size();
+  // Say so once when a stage has no fused stack kernel (channel counts other than 32 / 48 / 64 / 96 / 128 / 192 / 256
+  // after padding to 16, more than four blocks, dilations too wide for the tile): it then runs 2 launches per block
+  // on the generic conv kernel, several times slower — a different speed class, not an error.
+  if (cfg->num_res_blocks > 0 && !getenv("TTSB200_QUIET"))
+    for (int s = 0; s < cfg->n_stages; ++s)
+      if (stack_tiling(plan, s).kt == 0)
+        fprintf(stderr, "tts_b200: BF16 path: stage %d (%d channels, %d blocks) has no fused ResidualStack kernel; "
+                        "it will run %d generic conv launches (set TTSB200_QUIET=1 to silence)\n",
+                s, plan->stages[s].Cout, cfg->num_res_blocks, 2 * cfg->num_res_blocks);
 
   int prev = 0;
   cudaGetDevice(&prev);
