@@ -465,6 +465,35 @@ def test_bf16_persistent_ctas_walk_many_items(case, grid, monkeypatch):
     assert snr_db(generator_inference(spec, sd, mel, p), capped) >= BF16_SNR
 
 
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize("case", [0, 1, 3])
+def test_bf16_back_to_back_inferences_and_per_grid_waits(case, monkeypatch):
+    """Kernels hand work over per time segment and the kernels of the next inference are resident while
+    the previous one drains: many inferences enqueued without a host sync, on alternating inputs, must each give what a
+    lone call gives (a follower that mistook the previous inference's counts for its producer's showed up as a hang
+    and as stale tensors), and the same as a plan that waits for whole grids (TTSB200_NO_FOLLOW)."""
+    cls, kw, B, T, p = CASES[case]
+    m, spec, sd = default_init(cls, kw)
+    m.inference_padding = p
+    m.precision = "bf16"
+    g = torch.Generator().manual_seed(31)
+    mels = [torch.randn(B, spec.in_channels, T, generator=g).cuda() for _ in range(3)]
+    lone = []
+    for x in mels:
+        lone.append(m.inference(x).clone())
+        torch.cuda.synchronize()
+    outs = [m.inference(mels[i % 3]) for i in range(60)]          # no sync in between
+    torch.cuda.synchronize()
+    for i, y in enumerate(outs):
+        assert torch.equal(y, lone[i % 3]), i
+    monkeypatch.setenv("TTSB200_NO_FOLLOW", "1")                  # read once, at plan creation
+    m2, _, _ = default_init(cls, kw)
+    m2.inference_padding = p
+    m2.precision = "bf16"
+    for x, y in zip(mels, lone):
+        assert torch.equal(m2.inference(x), y)
+
+
 def test_bf16_full_size_cfg2_and_golden(golden):
     g = golden("mb_cfg2_item")
     m, spec, sd = default_init("multiband", {})
