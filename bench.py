@@ -693,6 +693,12 @@ def longform_arm(args):
         ms_g, wav_g = timed(replay, args.steps)
         if plan.describe()["launch"] == "cuda graph" and ms_g < ms:
             ms, wav = ms_g, wav_g
+    ms_f16 = None
+    if plan is not None:
+        # the waveform as fp16 (every reference caller ends in a 16-bit WAV): half the bytes over NVLink into rank 0
+        plan16 = longform.LongformPlan(model, T, batch=1, dtype=torch.float16)
+        ms_f16, _ = timed(plan16.graphed(mel), args.steps)
+        plan16.close()
     if rank == 0 or world == 1:
         assert wav is not None and wav.shape[-1] == n_out, (None if wav is None else wav.shape, n_out)
     value = n_out / (ms / 1e3)
@@ -708,6 +714,8 @@ def longform_arm(args):
     if world > 1:
         line["one_gpu_ms_same_run"] = ms1
         line["ms_per_step_eager_launches"] = ms_eager
+        line["f16_waveform"] = {"ms_per_step": ms_f16, "value": n_out / (ms_f16 / 1e3),
+                                "strong_efficiency": (ms1 / ms_f16) / world if ms1 else None}
         line["strong_efficiency"] = (ms1 / ms) / world if ms1 else None
         line["placement"] = plan.describe()
     if rank == 0:
