@@ -472,7 +472,12 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
-  pdl_launch_dependents();
+  if (!follow) {
+    pdl_launch_dependents();
+  } else if (tid == NTP - 1) {   // the counters are this inference's before the next kernel may launch (follow.cuh);
+    follow_armed(p.follow);      // a thread of the signal warp, so that no loader or issuer is held up
+    pdl_launch_dependents();
+  }
   if (warp != 0 && !follow) pdl_wait();   // warp 0 first starts the weight load (weights are written by no kernel)
 
   constexpr int PRODUCER2 = NT / 32;   // the extra warp: odd activation chunks
@@ -809,19 +814,22 @@ __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int
                                 int planes, int plane_rows, int halo, int* __restrict__ counters, int n_counters) {
   // one thread per (plane row, plane); row index covers halo margins too (reflect of the padded signal)
   //
-  // Hand-over counters (follow.cuh): block 0 zeroes them once the previous inference has completed, and only THEN
-  // lets the dependent kernels launch (a dependent launches when every CTA of this grid has triggered).  Without that
-  // order the next kernels — programmatic dependent launches cascade, so with small grids a whole inference can be
-  // resident while the previous one drains — would poll the previous inference's final counts, take them for their
-  // producer's and read tensors that have not been written yet.
+  // Hand-over counters (follow.cuh): block 0 zeroes them once the previous inference has completed; the armed flag
+  // behind them keeps the kernels that follow (resident early: dependent launches cascade) from polling before that.
   const bool zeroes = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
-  if (!zeroes) pdl_launch_dependents();
-  pdl_wait();
+  if (zeroes) {   // armed = 0 before ANY dependent can launch (follow.cuh follow_armed): counters[n_counters]
+    if (threadIdx.x == 0)
+      asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(counters + n_counters), "r"(0) : "memory");
+    __syncthreads();
+  }
+  pdl_launch_dependents();
+  pdl_wait();   // the previous inference on this stream has completed
   if (zeroes) {
     for (int i = threadIdx.x; i < n_counters; i += blockDim.x) counters[i] = 0;
     __threadfence();
     __syncthreads();
-    pdl_launch_dependents();
+    if (threadIdx.x == 0)
+      asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(counters + n_counters), "r"(1) : "memory");
   }
   const int L = T + 2 * pad;
   const int row = blockIdx.x * blockDim.x + threadIdx.x;

@@ -24,9 +24,29 @@ struct TcFollow {
   int units_per_seg;
   int n_units;            // per utterance
   int mult;               // counts per finished unit (column groups of the persistent conv kernel)
+  const int* armed;       // 1 once this inference's first kernel has zeroed the counters (follow_armed)
 };
 
 #ifdef __CUDACC__
+// The counters are zeroed by the first kernel of every inference, once the previous inference has completed.
+// Programmatic dependent launches cascade — with small grids a whole inference is resident while the previous one
+// drains — so a follower that polled early would take the previous inference's final counts for its producer's.
+// Protocol: the first kernel's block 0 stores armed = 0 BEFORE it lets its dependents launch, and armed = 1 after it
+// has waited for the previous inference and zeroed the counters; every following kernel's CTA waits for armed == 1
+// before IT lets its dependents launch.  A dependent launches when every CTA of its primary has triggered, so (a) no
+// kernel of the next inference can poll before its own first kernel has cleared the flag, and (b) when that happens
+// every CTA of the previous inference's followers has already passed its check.  The kernels that do not follow
+// (first conv of the chain, per-conv fallback) wait for whole grids and need neither.
+// One thread per CTA; the same thread executes griddepcontrol.launch_dependents afterwards.
+__device__ __forceinline__ void follow_armed(const TcFollow& f) {
+  for (;;) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f.armed) : "memory");
+    if (v == 1) break;
+    __nanosleep(64);
+  }
+}
+
 struct FollowState {
   int b = -1, seg = -1;   // segments up to `seg` of utterance `b` are known complete
 };

@@ -277,7 +277,7 @@ Bf16Workspace bf16_workspace(const ttsb200_plan* plan, int B, const Shape& sh) {
   w.head_floats = (size_t)round_up((int64_t)B * cfg.out_channels * sh.L.back(), 64);
   w.n_counters = (int)round_up((int64_t)(2 * cfg.n_stages + 2) * B * FOLLOW_SEGS, 64);
   w.total_bytes = (w.mel_elems + w.act_elems) * sizeof(__nv_bfloat16) + w.head_floats * sizeof(float) +
-                  (size_t)w.n_counters * sizeof(int);
+                  (size_t)(w.n_counters + 64) * sizeof(int);   // + the armed flag (follow.cuh follow_armed)
   return w;
 }
 
@@ -310,7 +310,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   auto counting = [&](int n_units, int unit_rows, int row_offset, int mult, int** done_out, int* units_per_seg) {
     *done_out = counters + (size_t)(n_counting++) * B * FOLLOW_SEGS;
     *units_per_seg = ceil_div(n_units, FOLLOW_SEGS);
-    return TcFollow{*done_out, unit_rows, row_offset, *units_per_seg, n_units, mult};
+    return TcFollow{*done_out, unit_rows, row_offset, *units_per_seg, n_units, mult, counters + wsz.n_counters};
   };
   cudaStream_t st = static_cast<cudaStream_t>(a->stream);
   Launcher ln{st, a->profile, B};

@@ -238,10 +238,15 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
-  pdl_launch_dependents();
-  // With done_in the previous kernel is followed utterance by utterance (the loader polls its counters) and nobody
+  // With follow.done the previous kernel is followed segment by segment (the loader polls its counters) and nobody
   // waits for its whole grid; what this kernel writes is then never a buffer the previous kernel still reads.
   const bool follow = p.follow.done != nullptr;
+  if (!follow) {
+    pdl_launch_dependents();
+  } else if (tid == 0) {   // the counters are this inference's before the next kernel may launch (follow.cuh)
+    follow_armed(p.follow);
+    pdl_launch_dependents();
+  }
   if (warp != PRODUCER_WARP && !follow) pdl_wait();   // the producer first prefetches weights (not written by any kernel)
 
   if (warp == PRODUCER_WARP) {
