@@ -71,6 +71,7 @@ __global__ void __launch_bounds__(NT) conv_f32_kernel(const ConvParams p) {
 
   float ra[BK / 2];
   float rw[CPT];
+  bool ra_lrelu = false;   // the prefetched slice still wants its LeakyReLU (applied in stash(), see fetch())
 
   auto fetch = [&](int it) {
     const int si = it >= its0 ? 1 : 0;
@@ -85,12 +86,13 @@ __global__ void __launch_bounds__(NT) conv_f32_kernel(const ConvParams p) {
     for (int i = 0; i < BK / 2; ++i) {
       const int c = c0 + lk + 2 * i;
       float v = 0.f;
-      if (col >= 0 && c < s.C) {
-        v = __ldg(xp + (int64_t)(2 * i) * s.Lreal);
-        if (s.lrelu) v = lrelu_f(v, p.slope);
-      }
+      // the raw value only: touching it here (the LeakyReLU prologue used to) makes the warp wait for the load
+      // BEFORE the FMAs of the current slice — half of all warp time in the kernel (ncu: long-scoreboard stalls on
+      // exactly that multiply); the activation is applied when the slice is stashed, after the FMAs
+      if (col >= 0 && c < s.C) v = __ldg(xp + (int64_t)(2 * i) * s.Lreal);
       ra[i] = v;
     }
+    ra_lrelu = s.lrelu != 0;
     const float* wp = s.w + ((int64_t)(ph * s.taps + j) * s.C + c0) * p.CoutPad + co0;
 #pragma unroll
     for (int i = 0; i < CPT; ++i) {
@@ -102,7 +104,7 @@ __global__ void __launch_bounds__(NT) conv_f32_kernel(const ConvParams p) {
   };
   auto stash = [&](int buf) {
 #pragma unroll
-    for (int i = 0; i < BK / 2; ++i) sA[buf][lk + 2 * i][lt] = ra[i];
+    for (int i = 0; i < BK / 2; ++i) sA[buf][lk + 2 * i][lt] = ra_lrelu ? lrelu_f(ra[i], p.slope) : ra[i];
 #pragma unroll
     for (int i = 0; i < CPT; ++i) {
       const int e = tid + NT * i;
