@@ -157,6 +157,8 @@ class LongformPlan:
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if mode == "local":          # this process alone, whatever group it belongs to (a one-GPU baseline inside a job)
+            self.world, self.rank, dst_rank, mode = 1, 0, 0, None
         self.dst_rank = int(dst_rank)
         self.p = int(generator.inference_padding)
         self.halo = receptive_halo_frames(generator) if halo is None else int(halo)
