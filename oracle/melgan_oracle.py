@@ -12,8 +12,9 @@ The reference expresses the generator as an ``nn.Sequential`` of stock torch mod
 arithmetic lives in torch's ATen CPU kernels (``requirements.txt:1`` pins only ``torch>=1.5``;
 this image has torch 2.11.0).  The oracle therefore works on a plain ``{key: tensor}`` state
 dict with the reference's key names and calls ``torch.nn.functional`` directly, in fp32 or
-fp64.  ``oracle/numpy_oracle.py`` is a second, ATen-free restatement used on small cases, and
-``oracle/c/melgan_ref.c`` a third in plain C.
+fp64.  ``oracle/numpy_oracle.py`` is a second, ATen-free restatement used on small cases;
+``oracle/bf16_emulation.py`` is the same graph with BF16 rounding where the CUDA path rounds; ``oracle/_ref``
+(``oracle/make_ref.py``) holds the unmodified reference modules themselves for the timed CPU baseline.
 
 Parity status: pinned by ``tests/golden/*.npz`` (made by ``oracle/gen_golden.py`` from the real
 reference) — see ``tests/test_oracle_golden.py``.
