@@ -473,12 +473,11 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
-  if (!follow) {
-    pdl_launch_dependents();
-  } else if (tid == NTP - 1) {   // the counters are this inference's before the next kernel may launch (follow.cuh);
-    follow_armed(p.follow);      // a thread of the signal warp, so that no loader or issuer is held up
-    pdl_launch_dependents();
+  if (follow) {   // the counters are this inference's before the next kernel may launch (follow.cuh follow_armed)
+    if (tid == 0) follow_armed(p.follow);
+    __syncthreads();
   }
+  pdl_launch_dependents();   // every thread: the CTA counts as triggered once all of its threads have
   if (warp != 0 && !follow) pdl_wait();   // warp 0 first starts the weight load (weights are written by no kernel)
 
   constexpr int PRODUCER2 = NT / 32;   // the extra warp: odd activation chunks

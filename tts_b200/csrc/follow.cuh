@@ -37,7 +37,8 @@ struct TcFollow {
 // kernel of the next inference can poll before its own first kernel has cleared the flag, and (b) when that happens
 // every CTA of the previous inference's followers has already passed its check.  The kernels that do not follow
 // (first conv of the chain, per-conv fallback) wait for whole grids and need neither.
-// One thread per CTA; the same thread executes griddepcontrol.launch_dependents afterwards.
+// One thread per CTA checks, a __syncthreads follows, then EVERY thread executes griddepcontrol.launch_dependents
+// (measured: with one thread triggering, the dependents launched only when the CTA exited — +3..5 % per kernel).
 __device__ __forceinline__ void follow_armed(const TcFollow& f) {
   for (;;) {
     int v;

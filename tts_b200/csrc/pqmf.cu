@@ -198,12 +198,11 @@ __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const 
   const int q0 = blockIdx.x * SF_TILE;
   const float* xb = x + (int64_t)b * 4 * Ts;
 
-  if (!follow.done) {
-    pdl_launch_dependents();
-  } else if (tid == 0) {   // the counters are this inference's before the next kernel may launch (follow.cuh)
-    follow_armed(follow);
-    pdl_launch_dependents();
+  if (follow.done) {   // the counters are this inference's before the next kernel may launch (follow.cuh follow_armed)
+    if (tid == 0) follow_armed(follow);
+    __syncthreads();
   }
+  pdl_launch_dependents();   // every thread: the CTA counts as triggered once all of its threads have
   if (tid < PQMF_FACT_TABLE) st[tid] = tbl[tid];
   // The head kernel counts finished chains per time segment (follow.cuh): follow it segment by segment when it
   // does, else wait for its whole grid.

@@ -243,12 +243,11 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   // With follow.done the previous kernel is followed segment by segment (the loader polls its counters) and nobody
   // waits for its whole grid; what this kernel writes is then never a buffer the previous kernel still reads.
   const bool follow = p.follow.done != nullptr;
-  if (!follow) {
-    pdl_launch_dependents();
-  } else if (tid == 0) {   // the counters are this inference's before the next kernel may launch (follow.cuh)
-    follow_armed(p.follow);
-    pdl_launch_dependents();
+  if (follow) {   // the counters are this inference's before the next kernel may launch (follow.cuh follow_armed)
+    if (tid == 0) follow_armed(p.follow);
+    __syncthreads();
   }
+  pdl_launch_dependents();   // every thread: the CTA counts as triggered once all of its threads have
   if (warp != PRODUCER_WARP && !follow) pdl_wait();   // the producer first prefetches weights (not written by any kernel)
 
   if (warp == PRODUCER_WARP) {
