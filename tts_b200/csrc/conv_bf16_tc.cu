@@ -473,7 +473,7 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = tmem_base_s;
-  if (follow) {   // the counters are this inference's before the next kernel may launch (follow.cuh follow_armed)
+  if (follow && !p.follow.early) {   // late form: the check precedes this CTA's trigger (follow.cuh follow_armed)
     if (tid == 0) follow_armed(p.follow);
     __syncthreads();
   }
@@ -811,13 +811,14 @@ __global__ void __launch_bounds__(NTS) tc_convs_kernel(const __grid_constant__ T
 
 // ---- layout helpers --------------------------------------------------------------------------------
 __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int pad, __nv_bfloat16* __restrict__ out,
-                                int planes, int plane_rows, int halo, int* __restrict__ counters, int n_counters) {
+                                int planes, int plane_rows, int halo, int* __restrict__ counters, int n_counters,
+                                int armed_id, int early) {
   // one thread per (plane row, plane); row index covers halo margins too (reflect of the padded signal)
   //
   // Hand-over counters (follow.cuh): block 0 zeroes them once the previous inference has completed; the armed flag
   // behind them keeps the kernels that follow (resident early: dependent launches cascade) from polling before that.
   const bool zeroes = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
-  if (zeroes) {   // armed = 0 before ANY dependent can launch (follow.cuh follow_armed): counters[n_counters]
+  if (zeroes && !early) {   // late form: armed = 0 before ANY dependent can launch (follow.cuh follow_armed)
     if (threadIdx.x == 0)
       asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(counters + n_counters), "r"(0) : "memory");
     __syncthreads();
@@ -829,7 +830,7 @@ __global__ void prep_mel_kernel(const float* __restrict__ mel, int C, int T, int
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0)
-      asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(counters + n_counters), "r"(1) : "memory");
+      asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(counters + n_counters), "r"(armed_id) : "memory");
   }
   const int L = T + 2 * pad;
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1039,13 +1040,14 @@ cudaError_t tc_conv_launch(const TcConvParams& p_in, int batch, const TcLaunchCt
 }
 
 cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out, int planes,
-                               int plane_rows, int halo, int* counters, int n_counters, cudaStream_t stream) {
+                               int plane_rows, int halo, int* counters, int n_counters, int armed_id, int early,
+                               cudaStream_t stream) {
   const dim3 grid(ceil_div(plane_rows, 128), planes, batch);
   // Launched behind the previous kernel of the stream like every other kernel of the chain: its CTAs are resident
   // when that kernel (the last one of the previous inference) drains, and griddepcontrol.wait inside holds them
   // until it has completed — which is also when its counters may be zeroed.
   return launch_pdl(prep_mel_kernel, grid, dim3(128), 0, stream, mel, C, T, pad, out, planes, plane_rows, halo, counters,
-                    n_counters);
+                    n_counters, armed_id, early);
 }
 
 cudaError_t tc_untile_launch(const __nv_bfloat16* x, int64_t batch_stride, int batch, int C, int64_t L, int plane_rows,

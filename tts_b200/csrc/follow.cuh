@@ -16,6 +16,9 @@
 namespace ttsb {
 
 constexpr int FOLLOW_SEGS = 32;   // counters per utterance and counting launch
+#ifndef FOLLOW_POLL_NS
+#define FOLLOW_POLL_NS 64          // back-off between polls of a counter
+#endif
 
 struct TcFollow {
   const int* done;        // producer's counters [batch][FOLLOW_SEGS]; nullptr = wait for the whole previous grid
@@ -24,27 +27,34 @@ struct TcFollow {
   int units_per_seg;
   int n_units;            // per utterance
   int mult;               // counts per finished unit (column groups of the persistent conv kernel)
-  const int* armed;       // 1 once this inference's first kernel has zeroed the counters (follow_armed)
+  const int* armed;       // == armed_id once this inference's first kernel has zeroed the counters (follow_armed)
+  int armed_id;
+  int early;              // the dependents may launch before the check (unique ids; see follow_armed)
 };
 
 #ifdef __CUDACC__
 // The counters are zeroed by the first kernel of every inference, once the previous inference has completed.
 // Programmatic dependent launches cascade — with small grids a whole inference is resident while the previous one
 // drains — so a follower that polled early would take the previous inference's final counts for its producer's.
-// Protocol: the first kernel's block 0 stores armed = 0 BEFORE it lets its dependents launch, and armed = 1 after it
-// has waited for the previous inference and zeroed the counters; every following kernel's CTA waits for armed == 1
-// before IT lets its dependents launch.  A dependent launches when every CTA of its primary has triggered, so (a) no
-// kernel of the next inference can poll before its own first kernel has cleared the flag, and (b) when that happens
-// every CTA of the previous inference's followers has already passed its check.  The kernels that do not follow
-// (first conv of the chain, per-conv fallback) wait for whole grids and need neither.
-// One thread per CTA checks, a __syncthreads follows, then EVERY thread executes griddepcontrol.launch_dependents
-// (measured: with one thread triggering, the dependents launched only when the CTA exited — +3..5 % per kernel).
+// The first kernel therefore publishes an `armed` word behind the zeroing and every follower waits for it.  Two forms:
+//  * early (ordinary launches): every inference has a process-wide unique id; the first kernel stores it after the
+//    zeroing and a follower's loader waits for exactly that value before its first poll.  The word holds the previous
+//    inference's id until then, and the first kernel overwrites it only after the previous inference has completed,
+//    when none of ITS followers can still be waiting.  Nothing holds the dependent launches back: the whole next
+//    inference may be resident, weights prefetched, while the previous one drains;
+//  * late (stream capture: a replayed graph carries the same id every time): the first kernel's block 0 stores 0
+//    BEFORE it lets its dependents launch and 1 after the zeroing; every following CTA waits for 1 before IT lets its
+//    dependents launch (one thread checks, __syncthreads, then every thread triggers — a CTA counts as triggered once
+//    all its threads have).  A dependent launches when every CTA of its primary has triggered, so no kernel of the next
+//    replay can poll before its own first kernel has cleared the word, and by then every follower CTA of the previous
+//    replay has passed its check.
+// The kernels that do not follow (first conv of the chain, per-conv fallback) wait for whole grids and need neither.
 __device__ __forceinline__ void follow_armed(const TcFollow& f) {
   for (;;) {
     int v;
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f.armed) : "memory");
-    if (v == 1) break;
-    __nanosleep(64);
+    if (v == f.armed_id) break;
+    __nanosleep(FOLLOW_POLL_NS);
   }
 }
 
@@ -61,6 +71,7 @@ __device__ __forceinline__ void follow_wait(const TcFollow& f, int b, int a0, in
   u0 = u0 < f.n_units ? u0 : f.n_units - 1;
   u1 = u1 < f.n_units ? u1 : f.n_units - 1;
   const int s0 = u0 / f.units_per_seg, s1 = u1 / f.units_per_seg;
+  if (st.b < 0 && f.early) follow_armed(f);   // first poll: the counters are this inference's from here on
   if (st.b != b) {
     st.b = b;
     st.seg = -1;
@@ -74,7 +85,7 @@ __device__ __forceinline__ void follow_wait(const TcFollow& f, int b, int a0, in
       int v;
       asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
       if (v >= target) break;
-      __nanosleep(64);
+      __nanosleep(FOLLOW_POLL_NS);
     }
   }
   st.seg = s1;

@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(SF_THREADS) pqmf_synth_4x63_fact_kernel(const 
   const int q0 = blockIdx.x * SF_TILE;
   const float* xb = x + (int64_t)b * 4 * Ts;
 
-  if (follow.done) {   // the counters are this inference's before the next kernel may launch (follow.cuh follow_armed)
+  if (follow.done && !follow.early) {   // late form: the check precedes this CTA's trigger (follow.cuh follow_armed)
     if (tid == 0) follow_armed(follow);
     __syncthreads();
   }

@@ -306,11 +306,22 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   // counters and what they reach when an utterance is complete; null when the last kernel does not count.
   TcFollow prod{};   // how the last launch counts its finished work; done == nullptr: it does not
   const bool follow_ok = !plan->ctx.no_follow;
+  // follow.cuh follow_armed: a unique id per inference, or — under stream capture, where a replay would carry the same
+  // id every time — the 0 / 1 form that holds the dependent launches back
+  cudaStreamCaptureStatus capture = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(static_cast<cudaStream_t>(a->stream), &capture);
+  const int armed_early = capture == cudaStreamCaptureStatusNone ? 1 : 0;
+  int armed_id = 1;
+  if (armed_early) {
+    static std::atomic<uint32_t> next_id{(uint32_t)std::chrono::steady_clock::now().time_since_epoch().count() * 2654435761u};
+    do armed_id = (int)next_id.fetch_add(1, std::memory_order_relaxed); while (armed_id == 0 || armed_id == 1);
+  }
   int n_counting = 0;   // counting launches so far: each gets its own [B][FOLLOW_SEGS] block of counters
   auto counting = [&](int n_units, int unit_rows, int row_offset, int mult, int** done_out, int* units_per_seg) {
     *done_out = counters + (size_t)(n_counting++) * B * FOLLOW_SEGS;
     *units_per_seg = ceil_div(n_units, FOLLOW_SEGS);
-    return TcFollow{*done_out, unit_rows, row_offset, *units_per_seg, n_units, mult, counters + wsz.n_counters};
+    return TcFollow{*done_out, unit_rows, row_offset, *units_per_seg, n_units, mult, counters + wsz.n_counters,
+                    armed_id, armed_early};
   };
   cudaStream_t st = static_cast<cudaStream_t>(a->stream);
   Launcher ln{st, a->profile, B};
@@ -379,7 +390,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     const CanonDims d = canon_dims(plan, cfg.in_channels, sh.L0);
     TTSB_CUDA(ln.run("bf16.prep.mel", 0, 0.0, 4.0 * B * cfg.in_channels * a->frames + 2.0 * B * d.elems, [&] {
       return tc_prep_mel_launch(a->mel, B, cfg.in_channels, a->frames, a->pad, melc, d.planes, d.rows, halo, counters,
-                                wsz.n_counters, st);
+                                wsz.n_counters, armed_id, armed_early, st);
     }));
   }
   {

@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
   // With follow.done the previous kernel is followed segment by segment (the loader polls its counters) and nobody
   // waits for its whole grid; what this kernel writes is then never a buffer the previous kernel still reads.
   const bool follow = p.follow.done != nullptr;
-  if (follow) {   // the counters are this inference's before the next kernel may launch (follow.cuh follow_armed)
+  if (follow && !p.follow.early) {   // late form: the check precedes this CTA's trigger (follow.cuh follow_armed)
     if (tid == 0) follow_armed(p.follow);
     __syncthreads();
   }

@@ -173,9 +173,10 @@ cudaError_t tc_conv_launch(const TcConvParams& p, int batch, const TcLaunchCtx& 
 
 // mel fp32 [B][C][T] -> canonical bf16 with replicate padding `pad` folded in and reflect margins
 // ... and zeroes `n_counters` hand-over counters (first kernel of a forward, ordered behind everything before it)
+// ... and publishes armed_id in counters[n_counters] (follow.cuh follow_armed; early = 0: the late form)
 cudaError_t tc_prep_mel_launch(const float* mel, int batch, int C, int T, int pad, __nv_bfloat16* out,
-                               int planes, int plane_rows, int halo, int* counters, int n_counters,
-                               cudaStream_t stream);
+                               int planes, int plane_rows, int halo, int* counters, int n_counters, int armed_id,
+                               int early, cudaStream_t stream);
 // canonical bf16 -> fp32 NCL (per-layer parity taps); undo_lrelu inverts a stored activation
 cudaError_t tc_untile_launch(const __nv_bfloat16* x, int64_t batch_stride, int batch, int C, int64_t L, int plane_rows,
                              int halo, int undo_lrelu, float slope, float* out, cudaStream_t stream);

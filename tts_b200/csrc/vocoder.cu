@@ -1,6 +1,8 @@
 // Host side of the C ABI (include/tts_b200.h): plan construction, the launch schedule of
 // generator.inference(), per-launch profiling and the host-buffer entry point.
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
