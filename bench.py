@@ -386,6 +386,14 @@ def gpu_arm(args):
     ms = allreduce_max(e0.elapsed_time(e1), world, dev)
     value = world * samples_per_step * args.steps / (ms * 1e-3)
     flops_per_sample = 2.0 * macs_per_item(FRAMES + 2 * PAD) / n_out   # 51,264
+    # The kernels of consecutive steps overlap: what the LAST timed step left in `out` must be what a
+    # lone call on the same input gives, bit for bit — a step that ran ahead of its producers would show here.
+    last_out = out.clone()
+    torch.cuda.synchronize(dev)
+    step(args.warmup + args.steps - 1)
+    torch.cuda.synchronize(dev)
+    consistent = bool(torch.equal(last_out, out))
+    assert consistent, "back-to-back steps differ from a lone call: kernels ran ahead of their producers"
 
     # per-launch CUDA-event pass over the same K steps -> every kernel against its own roofline
     prof = Profile()
@@ -518,7 +526,7 @@ def gpu_arm(args):
                        "l2": f"inputs rotate over a pool of {n_pool} batches = {n_pool * per_batch >> 20} MiB > 126 MiB L2",
                        "parallelism": f"{world} independent replicas, utterances sharded, no collective"},
             "roofline": roof, "whole_step": whole, "sustained": sustained, "roofline_by_kernel": table,
-            "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
+            "e2e": e2e, "back_to_back_equals_lone_call": consistent, "gpu_launches": launches_per_step * args.steps,
             "launches_per_step": launches_per_step, "clocks": clocks,
             "kernel_breakdown_ms_per_step": {f"{k[0]}@{k[1]}": round(v["ms"] / args.steps, 4)
                                              for k, v in sorted(fam.items(), key=lambda kv: -kv[1]["ms"])}}
