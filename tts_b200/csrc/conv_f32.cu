@@ -39,7 +39,7 @@ __device__ __forceinline__ int resolve_pos(const ConvSrc& s, int pos) {
 }
 
 template <int CPT>
-__global__ void __launch_bounds__(NT) conv_f32_kernel(const ConvParams p) {
+__global__ void __launch_bounds__(NT, CPT >= 6 ? 2 : (CPT >= 3 ? 3 : 4)) conv_f32_kernel(const ConvParams p) {
   constexpr int TM = 16 * CPT;
   __shared__ __align__(16) float sA[2][BK][TN];
   __shared__ __align__(16) float sW[2][BK][TM];
@@ -73,6 +73,16 @@ __global__ void __launch_bounds__(NT) conv_f32_kernel(const ConvParams p) {
   float rw[CPT];
   bool ra_lrelu = false;   // the prefetched slice still wants its LeakyReLU (applied in stash(), see fetch())
 
+  // loader constants of this thread: the K row and tile column of each of its CPT weight elements (e = tid + NT * i
+  // over a [BK][TM] slice), as one offset into the [k][CoutPad] weight rows
+  int wk[CPT], woff[CPT];
+#pragma unroll
+  for (int i = 0; i < CPT; ++i) {
+    const int e = tid + NT * i;
+    wk[i] = e / TM;
+    woff[i] = wk[i] * p.CoutPad + (e - wk[i] * TM);
+  }
+
   auto fetch = [&](int it) {
     const int si = it >= its0 ? 1 : 0;
     const ConvSrc& s = p.src[si];
@@ -81,36 +91,34 @@ __global__ void __launch_bounds__(NT) conv_f32_kernel(const ConvParams p) {
     const int j = r / nck;
     const int c0 = (r - j * nck) * BK;
     const int col = t_ok ? resolve_pos(s, t0 + lt + j * s.dil + s.shift + phase_shift) : -1;
-    const float* xp = s.x + (int64_t)b * s.batch_stride + (int64_t)(c0 + lk) * s.Lreal + col;
+    const bool full = c0 + BK <= s.C;   // uniform over the CTA: every channel of the slice exists (all but a last slice)
+    // the raw value only: touching it here (the LeakyReLU prologue used to) makes the warp wait for the load
+    // BEFORE the FMAs of the current slice — half of all warp time in the kernel (ncu: long-scoreboard stalls on
+    // exactly that multiply); the activation is applied when the slice is stashed, after the FMAs
+    const float* xp = s.x + (int64_t)b * s.batch_stride + (int64_t)(c0 + lk) * s.Lreal + (col >= 0 ? col : 0);
+    const int64_t xstep = 2 * (int64_t)s.Lreal;
+    if (full && col >= 0) {
 #pragma unroll
-    for (int i = 0; i < BK / 2; ++i) {
-      const int c = c0 + lk + 2 * i;
-      float v = 0.f;
-      // the raw value only: touching it here (the LeakyReLU prologue used to) makes the warp wait for the load
-      // BEFORE the FMAs of the current slice — half of all warp time in the kernel (ncu: long-scoreboard stalls on
-      // exactly that multiply); the activation is applied when the slice is stashed, after the FMAs
-      if (col >= 0 && c < s.C) v = __ldg(xp + (int64_t)(2 * i) * s.Lreal);
-      ra[i] = v;
+      for (int i = 0; i < BK / 2; ++i) ra[i] = __ldg(xp + i * xstep);
+    } else {
+#pragma unroll
+      for (int i = 0; i < BK / 2; ++i) ra[i] = (col >= 0 && c0 + lk + 2 * i < s.C) ? __ldg(xp + i * xstep) : 0.f;
     }
     ra_lrelu = s.lrelu != 0;
     const float* wp = s.w + ((int64_t)(ph * s.taps + j) * s.C + c0) * p.CoutPad + co0;
+    if (full) {
 #pragma unroll
-    for (int i = 0; i < CPT; ++i) {
-      const int e = tid + NT * i;
-      const int k = e / TM;
-      const int m = e - k * TM;
-      rw[i] = (c0 + k < s.C) ? __ldg(wp + (int64_t)k * p.CoutPad + m) : 0.f;
+      for (int i = 0; i < CPT; ++i) rw[i] = __ldg(wp + woff[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < CPT; ++i) rw[i] = (c0 + wk[i] < s.C) ? __ldg(wp + woff[i]) : 0.f;
     }
   };
   auto stash = [&](int buf) {
 #pragma unroll
     for (int i = 0; i < BK / 2; ++i) sA[buf][lk + 2 * i][lt] = ra_lrelu ? lrelu_f(ra[i], p.slope) : ra[i];
 #pragma unroll
-    for (int i = 0; i < CPT; ++i) {
-      const int e = tid + NT * i;
-      const int k = e / TM;
-      sW[buf][k][e - k * TM] = rw[i];
-    }
+    for (int i = 0; i < CPT; ++i) (&sW[buf][0][0])[tid + NT * i] = rw[i];   // [k][m] is linear in e = tid + NT * i
   };
 
   fetch(0);
