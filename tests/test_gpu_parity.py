@@ -494,6 +494,28 @@ def test_bf16_back_to_back_inferences_and_per_grid_waits(case, monkeypatch):
         assert torch.equal(m2.inference(x), y)
 
 
+@pytest.mark.timeout(300)
+def test_bf16_bench_shape_is_bit_reproducible():
+    """300 inferences of the bench shape (16 x 862 frames) enqueued back to back equal the lone calls bit for bit.
+    Guards a write-after-read hazard inside the fused ResidualStack kernel that only showed at this size, in about one
+    inference of a few hundred: epilogue 2 of tile t rewrote XA rows that tap 0 of tile t + 1 (same block) had not read
+    yet (stack_bf16_tc.cu, the d1_full[t + 1] wait; tests/cuda/stress_follow.py and stress_locate.py are the long forms)."""
+    m, spec, sd = default_init("multiband", {})
+    m.precision = "bf16"
+    g = torch.Generator().manual_seed(1)
+    mels = [torch.randn(16, 80, 862, generator=g).cuda() for _ in range(4)]
+    lone = []
+    for x in mels:
+        lone.append(m.inference(x).clone())
+        torch.cuda.synchronize()
+    bad = []
+    for start in range(0, 300, 30):
+        outs = [m.inference(mels[(start + j) % 4]) for j in range(30)]          # no sync in between
+        torch.cuda.synchronize()
+        bad += [start + j for j, y in enumerate(outs) if not torch.equal(y, lone[(start + j) % 4])]
+    assert not bad, bad
+
+
 def test_bf16_full_size_cfg2_and_golden(golden):
     g = golden("mb_cfg2_item")
     m, spec, sd = default_init("multiband", {})

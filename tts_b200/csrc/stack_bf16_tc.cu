@@ -955,6 +955,13 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
         // ---- epilogue 2: x_new = D2 -> XR[t] (raw) and XA (lrelu), or the stage output
         {
           mbar_wait(&bars.d2_full[t], ph);
+          // This tile's XA rows (and, at a sequence end, mirror rows inside the next tile) are about to be rewritten,
+          // and the NEXT tile's dilated-conv MMAs of this block read the last d of them (tap 0).  Nothing this warp has
+          // waited for covers those MMAs: d1_full[t] was committed before they were issued.  They are issued right
+          // behind it, a whole epilogue 1 + 1x1 round before this point, so the wait never spins — but a late issue
+          // (instruction-cache miss with several kernels resident, a starved warp) did let the rewrite win: one
+          // inference in a few hundred had d rows of one block computed from the block's OUTPUT.
+          if (KT > 1 && t + 1 < KT) mbar_wait(&bars.d1_full[t + 1], (n_d1 - 1) & 1);
           tc_fence_after();
           tr(220);
           trw(320);
