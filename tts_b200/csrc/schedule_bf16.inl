@@ -302,7 +302,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
   __nv_bfloat16* cur = nullptr;                  // the tensor the next launch reads
   float* headf = reinterpret_cast<float*>(act + wsz.act_elems);
   int* counters = reinterpret_cast<int*>(headf + wsz.head_floats);
-  // Hand-over between consecutive fused kernels utterance by utterance (tc_common.cuh wait_counter): the producer's
+  // Hand-over between consecutive fused kernels segment by segment (follow.cuh follow_wait): the producer's
   // counters and what they reach when an utterance is complete; null when the last kernel does not count.
   TcFollow prod{};   // how the last launch counts its finished work; done == nullptr: it does not
   const bool follow_ok = !plan->ctx.no_follow;
@@ -364,7 +364,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     p.trace_id = layer * 10 + trace_seq++ % 10;   // label for the debug timeline (trace.cuh)
     if (tc_conv_smem_bytes(p) > 224 * 1024)
       return fail(TTSB200_ERR_INVALID, std::string(name) + ": tile does not fit shared memory on the BF16 path");
-    // the persistent kernel counts finished units per utterance and follows a counting producer
+    // the persistent kernel counts finished units per (utterance, time segment) and follows a counting producer
     int n_units = 0, unit_rows = 0, row_offset = 0, mult = 0;
     const bool cnt = follow_ok && tc_conv_count_info(p, B, plan->ctx, &n_units, &unit_rows, &row_offset, &mult);
     TcFollow mine{};
@@ -540,7 +540,7 @@ int forward_bf16(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
         return rc;
     }
     if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
-    // the PQMF kernel follows a counting head kernel utterance by utterance
+    // the PQMF kernel follows a counting head kernel segment by segment
     if (int rc = finish_output(plan, a, ln, dst, to_out, Lin, head_done && prod.done ? &prod : nullptr)) return rc;
   }
   return 0;
