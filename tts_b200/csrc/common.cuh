@@ -88,9 +88,14 @@ struct ConvParams {
   float slope;
 };
 
-// cpt = output channels per thread (tile is 16*cpt channels x 128 time positions, 256 threads).
+// cpt = tile code (conv_f32.cu): 1..8 = output channels per thread of a 16*cpt-channel x 128-position tile, 24 / 32 / 48 = a
+// tile of exactly that many channels x 512 / 512 / 256 positions; 256 threads either way.
 int conv_f32_pick_cpt(int Cout);
+int conv_f32_tile_channels(int code);
 cudaError_t conv_f32_launch(const ConvParams& p, int batch, int cpt, cudaStream_t stream);
+// A centred 7-tap conv to <= 4 output channels (the output head) has a kernel of its own: conv_f32.cu head_f32_kernel.
+bool head_f32_usable(const ConvParams& p);
+cudaError_t head_f32_launch(const ConvParams& p, int batch, cudaStream_t stream);
 
 // ---- PQMF (pqmf.cu) ----------------------------------------------------------------------------
 // y: fp32, or fp16 when out_f16 (ttsb200_out_dtype).  crop (optional): only samples [lo, lo + len) of every row are

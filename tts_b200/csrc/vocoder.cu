@@ -47,7 +47,7 @@ struct BlobBuilder {
 void pack_conv(BlobBuilder& bb, ConvF32& c, const float* w, const float* b, int Cout, int Cin, int k) {
   c.Cin = Cin; c.Cout = Cout; c.taps = k; c.phases = 1;
   c.cpt = conv_f32_pick_cpt(Cout);
-  c.CoutPad = (int)round_up(Cout, 16 * c.cpt);
+  c.CoutPad = (int)round_up(Cout, conv_f32_tile_channels(c.cpt));
   c.w_off = bb.alloc((size_t)k * Cin * c.CoutPad);
   c.b_off = bb.alloc(c.CoutPad);
   for (int o = 0; o < Cout; ++o)
@@ -63,7 +63,7 @@ void pack_conv(BlobBuilder& bb, ConvF32& c, const float* w, const float* b, int 
 void pack_convT(BlobBuilder& bb, ConvF32& c, const float* w, const float* b, int Cin, int Cout, int f, int P) {
   c.Cin = Cin; c.Cout = Cout; c.taps = 2; c.phases = f;
   c.cpt = conv_f32_pick_cpt(Cout);
-  c.CoutPad = (int)round_up(Cout, 16 * c.cpt);
+  c.CoutPad = (int)round_up(Cout, conv_f32_tile_channels(c.cpt));
   c.w_off = bb.alloc((size_t)f * 2 * Cin * c.CoutPad);
   c.b_off = bb.alloc(c.CoutPad);
   for (int r = 0; r < f; ++r) {
@@ -313,7 +313,7 @@ int forward_f32(const ttsb200_plan* plan, const ttsb200_forward_args* a) {
     TTSB_CUDA(ln.run("f32.head.k7+tanh", ih, 2 * macs,
                      io_bytes((double)Cl * Lin, (double)cfg.out_channels * Lin,
                               (double)cfg.proj_kernel * Cl * cfg.out_channels),
-                     [&] { return conv_f32_launch(p, B, plan->head.cpt, st); }));
+                     [&] { return head_f32_usable(p) ? head_f32_launch(p, B, st) : conv_f32_launch(p, B, plan->head.cpt, st); }));
     if (int rc = copy_tap(a, ih + 1, dst, cfg.out_channels, Lin, st)) return rc;
     if (int rc = finish_output(plan, a, ln, dst, to_out, Lin)) return rc;
   }
