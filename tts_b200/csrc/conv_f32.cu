@@ -328,7 +328,7 @@ cudaError_t head_f32_launch(const ConvParams& p, int batch, cudaStream_t stream)
 
 // Tile codes: 1, 2, 3, 4, 6, 8 = that many channels per thread in 16 groups (tile 16 * code channels x 128 positions, K
 // slices of 16); 24 / 32 / 48 = a tile of exactly that many channels in 4 / 4 / 8 groups of 6 / 8 / 6 (512 / 512 / 256
-// positions, K slices of 8).
+// positions, K slices of 8 / 8 / 16).
 int conv_f32_tile_channels(int code) { return code >= 24 ? code : 16 * code; }
 
 int conv_f32_pick_cpt(int Cout) {
@@ -368,7 +368,7 @@ cudaError_t conv_f32_launch(const ConvParams& p, int batch, int cpt, cudaStream_
     case 8: return launch_tile<8, 16, 16>(p, batch, stream);
     case 24: return launch_tile<6, 4, 8>(p, batch, stream);
     case 32: return launch_tile<8, 4, 8>(p, batch, stream);
-    case 48: return launch_tile<6, 8, 8>(p, batch, stream);
+    case 48: return launch_tile<6, 8, 16>(p, batch, stream);
     default: return cudaErrorInvalidValue;
   }
 }
