@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(NT) head_f32_kernel(const ConvParams p) {
 bool head_f32_usable(const ConvParams& p) {
   const ConvSrc& s = p.src[0];
   return p.nsrc == 1 && p.n_phase == 1 && p.out_stride == 1 && p.Cout <= 4 && s.C <= HEAD_MAX_C && s.taps == HEAD_TAPS &&
-         s.dil == 1 && s.shift == -(HEAD_TAPS - 1) / 2 && s.L > HEAD_TAPS;
+         s.dil == 1 && s.shift == -(HEAD_TAPS - 1) / 2 && s.L > HEAD_TAPS && p.Lt == s.L;
 }
 
 cudaError_t head_f32_launch(const ConvParams& p, int batch, cudaStream_t stream) {
