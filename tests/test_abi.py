@@ -101,3 +101,32 @@ def test_pqmf_factorisation_matches_oracle():
     rnd = np.random.default_rng(0).standard_normal((4, 63)).astype(np.float32)
     assert lib.ttsb200_pqmf_factor_4x63(rnd.ctypes.data, tbl.ctypes.data) == 0
     assert lib.ttsb200_pqmf_factor_4x63(None, tbl.ctypes.data) < 0
+
+
+def test_shipped_library_is_sm100a_tcgen05_code():
+    """The library that travels to the GPU box holds sm_100a code whose hot kernels carry tcgen05 MMAs (UTCHMMA), TMEM
+    loads / stores (LDTM / STTM) and bulk copies (UBLKCP) — a build that lost the tensor-core path would still load and
+    export every symbol.  Static check with cuobjdump (part of the CUDA toolkit; skipped where it is absent)."""
+    import shutil
+    import subprocess
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    elf = subprocess.run(["cuobjdump", "-lelf", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in elf, elf
+    sass = subprocess.run(["cuobjdump", "-sass", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    per_kernel, cur = {}, None
+    for line in sass.splitlines():
+        m = re.match(r"\s*Function : (\S+)", line)
+        if m:
+            cur = per_kernel.setdefault(m.group(1), set())
+            continue
+        m = re.match(r"\s*/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_]*)", line)
+        if m and cur is not None:
+            cur.add(m.group(1))
+    stack = [ops for name, ops in per_kernel.items() if "tc_stack_kernel" in name]
+    convp = [ops for name, ops in per_kernel.items() if "tc_convp_kernel" in name]
+    assert len(stack) >= 10 and convp
+    for ops in stack + convp:
+        assert {"UTCHMMA", "UBLKCP"} <= ops, ops
+    assert all({"LDTM", "STTM"} <= ops for ops in stack)
+    assert not any("HMMA" in ops for ops in per_kernel.values())        # no mma.sync fallback anywhere
