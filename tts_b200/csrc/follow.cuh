@@ -19,6 +19,9 @@ constexpr int FOLLOW_SEGS = 32;   // counters per utterance and counting launch
 #ifndef FOLLOW_POLL_NS
 #define FOLLOW_POLL_NS 64          // back-off between polls of a counter
 #endif
+#ifndef FOLLOW_TIMEOUT_NS
+#define FOLLOW_TIMEOUT_NS 20000000000ull   // a follower that has polled this long traps instead of hanging the GPU
+#endif
 
 struct TcFollow {
   const int* done;        // producer's counters [batch][FOLLOW_SEGS]; nullptr = wait for the whole previous grid
@@ -49,12 +52,30 @@ struct TcFollow {
 //    replay can poll before its own first kernel has cleared the word, and by then every follower CTA of the previous
 //    replay has passed its check.
 // The kernels that do not follow (first conv of the chain, per-conv fallback) wait for whole grids and need neither.
+// Watchdog of the poll loops: a producer that never counts (a bug, or a kernel of the chain that was never launched)
+// must surface as a CUDA error, not as a device that spins for ever.  Every 4,096 polls (a few ms) the global timer is
+// read; FOLLOW_TIMEOUT_NS (20 s: four orders of magnitude above the longest legitimate wait, a whole previous
+// inference) after the first reading the thread traps.  Costs nothing on a wait that is already satisfied.
+struct FollowPatience {
+  uint32_t polls = 0;
+  unsigned long long t0 = 0;
+  __device__ __forceinline__ void tick() {
+    if ((++polls & 4095u) != 0) return;
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > FOLLOW_TIMEOUT_NS) __trap();
+  }
+};
+
 __device__ __forceinline__ void follow_armed(const TcFollow& f) {
+  FollowPatience patience;
   for (;;) {
     int v;
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f.armed) : "memory");
     if (v == f.armed_id) break;
     __nanosleep(FOLLOW_POLL_NS);
+    patience.tick();
   }
 }
 
@@ -81,11 +102,13 @@ __device__ __forceinline__ void follow_wait(const TcFollow& f, int b, int a0, in
     const int left = f.n_units - s * f.units_per_seg;
     const int target = (left < f.units_per_seg ? left : f.units_per_seg) * f.mult;
     const int* p = f.done + b * FOLLOW_SEGS + s;
+    FollowPatience patience;
     for (;;) {
       int v;
       asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
       if (v >= target) break;
       __nanosleep(FOLLOW_POLL_NS);
+      patience.tick();
     }
   }
   st.seg = s1;
