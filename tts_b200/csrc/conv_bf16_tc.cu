@@ -432,7 +432,8 @@ constexpr int NTP = NT + 64;   // + second activation producer, + the warp that 
 __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ TcConvParams p, const int nslots,
                                                        const int n_tiles, const int batch) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bar_w, a_full[CP_MAX_SLOTS], a_empty[CP_MAX_SLOTS], acc_full[2], acc_free[2], unit_done[2];
+  __shared__ __align__(8) uint64_t bar_w, a_full[CP_MAX_SLOTS], a_empty[CP_MAX_SLOTS], acc_full[2], acc_free[2];
+  __shared__ uint32_t units_done[2];   // epilogue warps that have issued their stores, summed over the even / odd units
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float s_bias[256];
 
@@ -463,8 +464,7 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_free[i], EPI_THREADS);
     }
-    mbar_init(&unit_done[0], EPI_THREADS / 32);   // two in turn: the signal warp may lag by up to three units
-    mbar_init(&unit_done[1], EPI_THREADS / 32);
+    units_done[0] = units_done[1] = 0;
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc(&tmem_base_s, 2 * acc_stride);
@@ -489,7 +489,7 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
       int i = 0;
       for (int u = first; u < n_units; u += stride, ++i) {
         const int b = u / n_tiles, tile = u - b * n_tiles;
-        mbar_wait(&unit_done[i & 1], (i >> 1) & 1);
+        smem_count_wait(&units_done[i & 1], (uint32_t)((i >> 1) + 1) * (EPI_THREADS / 32));
         __threadfence();
         atomicAdd(p.done_out + b * FOLLOW_SEGS + tile / p.count_units_per_seg, 1);
       }
@@ -586,7 +586,7 @@ __global__ void __launch_bounds__(NTP) tc_convp_kernel(const __grid_constant__ T
       mbar_arrive(&acc_free[buf]);
       if (p.done_out) {
         __syncwarp();
-        if (lane == 0) mbar_arrive(&unit_done[i & 1]);
+        if (lane == 0) smem_count_add(&units_done[i & 1]);
       }
       tr(31);
     }

@@ -74,8 +74,9 @@ struct Bars {
   uint64_t xa_ready[MAX_KT], xr_ready[MAX_KT], d1_full[MAX_KT], h_ready[MAX_KT], d2_full[MAX_KT];
   uint64_t ring_full[RING_MAX_SLOTS], ring_empty[RING_MAX_SLOTS];
   uint64_t edge[4 * MAX_KT];   // fused head: warp w's first / last three accumulator rows are in the edge buffer
-  uint64_t item_done[2];       // every epilogue warp has issued its stores of the item (-> the signal warp); two
-                               // barriers in turn, so the signal warp may lag its CTA by up to three items
+  uint32_t items_done[2];      // epilogue warps that have issued their stores, summed over the even / odd items (->
+                               // the signal warp; tc_common.cuh smem_count_add: counters, not parity barriers, so the
+                               // signal warp may lag its CTA by any number of items)
 };
 
 // TAIL: what follows the last block — 0 the stack output is stored, 1 fused output head, 2 fused transposed conv
@@ -198,8 +199,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       mbar_init(&bars.ring_empty[i], 1);
     }
     for (int i = 0; i < 4 * MAX_KT; ++i) mbar_init(&bars.edge[i], 32);
-    mbar_init(&bars.item_done[0], KT * CS * 4);
-    mbar_init(&bars.item_done[1], KT * CS * 4);
+    bars.items_done[0] = bars.items_done[1] = 0;
     for (int t = 0; t < KT; ++t) {
       mbar_init(&bars.xa_ready[t], GROUP_THREADS);
       mbar_init(&bars.xr_ready[t], GROUP_THREADS);
@@ -654,7 +654,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
         const int item = blockIdx.x + it * gridDim.x;
         const int b = item / p.n_chains, chain = item - b * p.n_chains;
-        mbar_wait(&bars.item_done[it & 1], (it >> 1) & 1);
+        smem_count_wait(&bars.items_done[it & 1], (uint32_t)((it >> 1) + 1) * (KT * CS * 4));
         __threadfence();
         atomicAdd(p.done_out + b * FOLLOW_SEGS + chain / p.count_units_per_seg, 1);
       }
@@ -1150,7 +1150,7 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
       auto signal_item = [&]() {   // this warp's stores of the item are out: count it for utterance b
         if (p.done_out) {
           __syncwarp();
-          if (lane == 0) mbar_arrive(&bars.item_done[it & 1]);
+          if (lane == 0) smem_count_add(&bars.items_done[it & 1]);
         }
       };
       if (up) {

@@ -94,6 +94,27 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
   }
 }
 
+// ---- a lossless hand-off from the epilogue warps to the signal warp -----------------------------------------------
+// The signal warp of a counting kernel (follow.cuh) publishes each finished work unit once EVERY epilogue warp has
+// issued the unit's stores.  An mbarrier pair told it so at first, waited on by parity: a parity cannot tell phase n
+// from n + 2, so a signal thread that fell three units behind (its fence waits for the CTA's stores to drain) would
+// have waited for a phase that had come and gone — at the end of the kernel for ever, and the follower with it.
+// Monotonic counters in shared memory cannot be overrun: each epilogue warp adds one per unit with release semantics
+// after its stores, to the counter of the unit's parity (epilogue warps are never two units apart: the accumulator /
+// the x tile of unit n + 2 is released only when every warp has finished unit n — but they may be one apart), and
+// the signal thread acquires `count[n & 1] >= (n / 2 + 1) * warps`.
+__device__ __forceinline__ void smem_count_add(uint32_t* c) {
+  asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(smem_u32(c)) : "memory");
+}
+__device__ __forceinline__ void smem_count_wait(uint32_t* c, uint32_t target) {
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(c)) : "memory");
+    if (v >= target) break;
+    __nanosleep(64);
+  }
+}
+
 // ---- bulk async copy global -> shared (TMA engine, no tensor map) -------------------------------
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
