@@ -647,8 +647,8 @@ __global__ void __launch_bounds__(SERVICE_THREADS + KT * CS * 128, (KT * 5 * CP 
     }
   } else if (warp == SIGNAL_WARP) {
     // =============================== signal warp ===============================
-    // Item by item: once every epilogue warp has issued its stores (item_done: their arrive releases them to this
-    // thread), make them visible device-wide and count the item for its utterance.  The next kernel's loader polls
+    // Item by item: once every epilogue warp has issued its stores (items_done: their release add hands them to this
+    // thread's acquire), make them visible device-wide and count the item for its utterance.  The next kernel's loader polls
     // that counter (follow.cuh follow_wait) instead of waiting for this whole grid.
     if (p.done_out && elect_one()) {
       for (int it = 0; blockIdx.x + it * gridDim.x < n_items; ++it) {
